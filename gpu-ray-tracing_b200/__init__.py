@@ -1,0 +1,17 @@
+"""gpu-ray-tracing_b200 -- Blackwell-native ray-casting core behind the reference's own interface.
+
+The compute lives in libb2rt.so (hand-written CUDA for sm_100a, C ABI in include/b2rt.h); this
+package is the thin Python host side: same names as the reference's C++ classes for the path
+(CudaTracer.traceBatch, RayBuffer.mortonSort, RayGen.primary/ao, CudaBVH, Renderer ...).
+Import it with importlib (the directory name has a hyphen):
+
+    import importlib; b2rt = importlib.import_module("gpu-ray-tracing_b200")
+"""
+from ._lib import (B2rtError, EXPORTS, KEY_DTYPE, LAYOUT_COMPACT2, LIB_PATH, RAY_DTYPE, RESULT_DTYPE,
+                   TRACE_ANY_HIT, TRACE_STATS, TRACE_WRITE_BARY, lib)
+from .host import (BVH, Context, CudaBVH, CudaTracer, PixelTable, RayBuffer, RayGen, Renderer, Scene,
+                   camera_matrices, countHits, fail)
+
+__all__ = ["B2rtError", "BVH", "Context", "CudaBVH", "CudaTracer", "EXPORTS", "KEY_DTYPE", "LAYOUT_COMPACT2",
+           "LIB_PATH", "PixelTable", "RAY_DTYPE", "RESULT_DTYPE", "RayBuffer", "RayGen", "Renderer", "Scene",
+           "TRACE_ANY_HIT", "TRACE_STATS", "TRACE_WRITE_BARY", "camera_matrices", "countHits", "fail", "lib"]

@@ -1,0 +1,110 @@
+"""ctypes binding of libb2rt.so (include/b2rt.h).  No CPU fallback: if the library is missing or a
+call fails, an exception is raised -- nothing in this package computes a result any other way."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb2rt.so")
+
+LAYOUT_COMPACT2 = 5
+TRACE_ANY_HIT = 1
+TRACE_WRITE_BARY = 2
+TRACE_STATS = 4
+
+RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmin", "<f4"), ("d", "<f4", 3), ("tmax", "<f4")])
+RESULT_DTYPE = np.dtype([("id", "<i4"), ("t", "<f4"), ("padA", "<i4"), ("padB", "<i4")])
+KEY_DTYPE = np.dtype([("oldSlot", "<i4"), ("hash", "<u4", 6)])
+
+
+class B2rtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("b2rt error %d: %s" % (code, msg))
+        self.code = code
+
+
+class TraceStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("node_iters", "node_lanes", "tri_iters", "tri_lanes", "fetches", "rays")]
+
+
+class TraceConfig(C.Structure):
+    _fields_ = [("top_nodes", C.c_int), ("fetch_threshold", C.c_int), ("blocks_per_sm", C.c_int), ("variant", C.c_int)]
+
+
+class BuildParams(C.Structure):
+    _fields_ = [("split_alpha", C.c_float), ("min_leaf", C.c_int), ("max_leaf", C.c_int), ("threads", C.c_int),
+                ("spatial_splits", C.c_int)]
+
+
+_lib = None
+
+vp = C.c_void_p
+i32 = C.c_int
+i64 = C.c_int64
+f32 = C.c_float
+u32 = C.c_uint32
+sz = C.c_size_t
+
+_SIGNATURES = {
+    "b2rt_create": (i32, [i32, C.POINTER(vp)]),
+    "b2rt_destroy": (None, [vp]),
+    "b2rt_last_error": (C.c_char_p, [vp]),
+    "b2rt_launch_count": (i64, [vp]),
+    "b2rt_set_trace_config": (i32, [vp, C.POINTER(TraceConfig)]),
+    "b2rt_device_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "b2rt_set_bvh": (i32, [vp, vp, sz, vp, sz, vp, sz, i32, i32]),
+    "b2rt_get_bvh": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]),
+    "b2rt_trace": (i32, [vp, vp, vp, i64, C.c_uint, vp, C.POINTER(f32)]),
+    "b2rt_trace_host": (i32, [vp, vp, vp, i64, C.c_uint, C.POINTER(f32), C.POINTER(f32)]),
+    "b2rt_get_trace_stats": (i32, [vp, C.POINTER(TraceStats)]),
+    "b2rt_raygen_primary": (i32, [vp, vp, vp, i32, i32, f32, vp, vp, vp, vp, vp]),
+    "b2rt_raygen_ao": (i32, [vp, i32, i32, i32, f32, u32, vp, vp, vp, vp, vp, vp, vp]),
+    "b2rt_morton_sort": (i32, [vp, vp, vp, vp, i64, vp, vp]),
+    "b2rt_find_aabb": (i32, [vp, vp, i64, vp, vp]),
+    "b2rt_morton_keys": (i32, [vp, vp, i64, vp, vp, vp]),
+    "b2rt_count_hits": (i32, [vp, vp, i64, C.POINTER(i64), vp]),
+    "b2rt_reconstruct": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "b2rt_pixel_table": (i32, [i32, i32, vp, vp]),
+    "b2rt_camera_matrices": (i32, [vp, vp, vp, f32, f32, f32, i32, i32, vp, vp]),
+    "b2rt_bvh_build": (i32, [vp, i32, vp, i32, C.POINTER(BuildParams), C.POINTER(vp)]),
+    "b2rt_bvh_free": (None, [vp]),
+    "b2rt_bvh_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]),
+    "b2rt_bvh_stats": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(f32), C.POINTER(i32)]),
+    "b2rt_bvh_save": (i32, [vp, C.c_char_p]),
+    "b2rt_bvh_load": (i32, [C.c_char_p, C.POINTER(vp)]),
+    "b2rt_tri_normals": (i32, [vp, vp, i32, vp]),
+    "b2rt_scene_generate": (i32, [i32, i32, C.c_uint64, C.POINTER(vp)]),
+    "b2rt_scene_free": (None, [vp]),
+    "b2rt_scene_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(i32), C.POINTER(vp), C.POINTER(i32)]),
+    "b2rt_scene_camera": (i32, [vp, vp]),
+    "b2rt_scene_write_obj": (i32, [vp, C.c_char_p]),
+}
+
+EXPORTS = sorted(_SIGNATURES)
+
+
+def lib():
+    """The loaded library.  Raises if libb2rt.so has not been built (python gpu-ray-tracing_b200/build.py)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("libb2rt.so is not built: run `python gpu-ray-tracing_b200/build.py` "
+                              "(there is no CPU fallback)")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def check(rc, ctx=None):
+    if rc != 0:
+        msg = lib().b2rt_last_error(ctx)
+        raise B2rtError(rc, msg.decode() if msg else "")
+
+
+def np_ptr(a):
+    return a.ctypes.data_as(vp)

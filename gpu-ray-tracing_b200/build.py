@@ -1,0 +1,80 @@
+"""Builds gpu-ray-tracing_b200/libb2rt.so in-tree with nvcc for sm_100a (no JIT cache, no fallback).
+
+    python gpu-ray-tracing_b200/build.py [--force] [--verbose]
+
+nvcc cross-compiles without a GPU, so this runs in the CPU-only container as well as on the
+B200 box (where the prebuilt .so that travelled with the snapshot is normally used as is).
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
+LIB = os.path.join(HERE, "libb2rt.so")
+INCLUDE = os.path.join(os.path.dirname(HERE), "include")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+CXX = os.environ.get("CXX", "g++")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+NVCC_COMMON = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-I", INCLUDE]
+
+# (source, extra flags).  -fmad=false: values that feed parity tests bit-for-bit (ray generation,
+# Morton keys, pixel reconstruction) must not depend on FMA contraction; the traversal kernel
+# spells out every FMA itself.
+CUDA_SOURCES = [
+    ("trace.cu", ["-Xptxas", "-v"]),
+    ("api.cu", []),
+    ("raygen.cu", ["-fmad=false"]),
+    ("raysort.cu", ["-fmad=false"]),
+    ("misc.cu", ["-fmad=false"]),
+]
+HOST_SOURCES = ["host/bvh_builder.cpp", "host/scenegen.cpp", "host/host_util.cpp"]
+HOST_FLAGS = ["-O2", "-ffp-contract=off", "-fPIC", "-std=c++17", "-pthread", "-Wall", "-I", INCLUDE]
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.getmtime(d) <= t for d in deps)
+
+
+def _run(cmd, verbose):
+    if verbose:
+        print(" ".join(cmd), flush=True)
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("build step failed: " + " ".join(cmd))
+    return r.stdout + r.stderr
+
+
+def build(force=False, verbose=False):
+    os.makedirs(OBJ, exist_ok=True)
+    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(INCLUDE, "b2rt.h"), os.path.abspath(__file__)]
+    objs = []
+    log = []
+    for src, extra in CUDA_SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(OBJ, src.replace("/", "_") + ".o")
+        objs.append(o)
+        if force or not _newer(o, [s] + headers):
+            log.append(_run([NVCC] + NVCC_COMMON + extra + ["-c", s, "-o", o], verbose))
+    for src in HOST_SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(OBJ, src.replace("/", "_") + ".o")
+        objs.append(o)
+        if force or not _newer(o, [s] + headers):
+            log.append(_run([CXX] + HOST_FLAGS + ["-c", s, "-o", o], verbose))
+    if force or not _newer(LIB, objs):
+        log.append(_run([NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lpthread"], verbose))
+    with open(os.path.join(OBJ, "build.log"), "a") as f:
+        f.write("".join(log))
+    return LIB
+
+
+if __name__ == "__main__":
+    lib = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    print(lib)

@@ -1,0 +1,287 @@
+// api.cu -- context, BVH upload and the trace entry points of the C ABI (include/b2rt.h).
+#include "common.cuh"
+
+#include <stdarg.h>
+
+#include <algorithm>
+#include <queue>
+#include <vector>
+
+namespace b2rt {
+
+std::string g_createError;
+
+int setError(b2rt_ctx* ctx, int code, const char* fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->lastError = buf; else g_createError = buf;
+    return code;
+}
+
+int ensureScratch(b2rt_ctx* ctx, size_t bytes)
+{
+    if (bytes <= ctx->scratchBytes) return B2RT_OK;
+    if (ctx->scratch) { cudaFree(ctx->scratch); ctx->scratch = nullptr; ctx->scratchBytes = 0; }
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->scratch, bytes));
+    ctx->scratchBytes = bytes;
+    return B2RT_OK;
+}
+
+static int ensureStage(b2rt_ctx* ctx, size_t bytes)
+{
+    if (bytes <= ctx->stageBytes) return B2RT_OK;
+    if (ctx->stage) { cudaFree(ctx->stage); ctx->stage = nullptr; ctx->stageBytes = 0; }
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->stage, bytes));
+    ctx->stageBytes = bytes;
+    return B2RT_OK;
+}
+
+// How many leading nodes of the private copy are ordered "most likely visited first".
+constexpr int kMaxTopNodes = 2048;
+
+// Re-lay the node array: the kMaxTopNodes nodes with the largest boxes (a greedy descent from the
+// root by surface area, i.e. by SAH visit probability) come first, the rest keep their order.
+// Child references (float4 indices, CudaBVH.cc:303) are rewritten; leaf references (~woop row,
+// CudaBVH.cc:312) are untouched, so hit indices still address the caller's Woop / triIndex rows.
+static void relayoutNodes(const std::vector<float>& in, std::vector<float>& out, int& topCount)
+{
+    const int n = (int)(in.size() / 16);
+    out.resize(in.size());
+    topCount = 0;
+    if (n == 0) return;
+    auto childArea = [&](int node, int c) -> float {
+        const float* p = &in[(size_t)node * 16];
+        float dx, dy, dz;
+        if (c == 0) { dx = p[1] - p[0]; dy = p[3] - p[2]; dz = p[9] - p[8]; }
+        else        { dx = p[5] - p[4]; dy = p[7] - p[6]; dz = p[11] - p[10]; }
+        return dx * dy + dy * dz + dz * dx;
+    };
+    std::vector<int> order; order.reserve(n);
+    std::vector<char> placed(n, 0);
+    typedef std::pair<float, int> Item;
+    std::priority_queue<Item> pq;
+    pq.push(Item(3.0e38f, 0));
+    const int want = std::min(n, kMaxTopNodes);
+    while (!pq.empty() && (int)order.size() < want) {
+        const int node = pq.top().second; pq.pop();
+        if (placed[node]) continue;
+        placed[node] = 1; order.push_back(node);
+        int32_t ch[2]; memcpy(ch, &in[(size_t)node * 16 + 12], 8);
+        for (int c = 0; c < 2; c++)
+            if (ch[c] >= 0 && ch[c] / 4 < n) pq.push(Item(childArea(node, c), ch[c] / 4));
+    }
+    topCount = (int)order.size();
+    for (int i = 0; i < n; i++) if (!placed[i]) order.push_back(i);
+    std::vector<int> newIndex(n);
+    for (int i = 0; i < n; i++) newIndex[order[i]] = i;
+    for (int i = 0; i < n; i++) {
+        const float* src = &in[(size_t)order[i] * 16];
+        float* dst = &out[(size_t)i * 16];
+        memcpy(dst, src, 64);
+        int32_t ch[4]; memcpy(ch, src + 12, 16);
+        for (int c = 0; c < 2; c++)
+            if (ch[c] >= 0 && ch[c] / 4 < n) ch[c] = newIndex[ch[c] / 4] * 4;
+        memcpy(dst + 12, ch, 16);
+    }
+}
+
+}  // namespace b2rt
+
+using namespace b2rt;
+
+extern "C" {
+
+int b2rt_create(int device, b2rt_ctx** out)
+{
+    if (!out) return setError(nullptr, B2RT_ERR_ARG, "b2rt_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return setError(nullptr, B2RT_ERR_NO_DEVICE, "b2rt_create: no CUDA device (%s)", cudaGetErrorString(e));
+    if (device < 0 || device >= count)
+        return setError(nullptr, B2RT_ERR_ARG, "b2rt_create: device %d out of range [0,%d)", device, count);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess)
+        return setError(nullptr, B2RT_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+    if (prop.major != 10)
+        return setError(nullptr, B2RT_ERR_NO_DEVICE,
+                        "b2rt_create: device %d is sm_%d%d; this library carries sm_100a code only (no fallback)",
+                        device, prop.major, prop.minor);
+    b2rt_ctx* ctx = new b2rt_ctx();
+    ctx->device = device;
+    ctx->smCount = prop.multiProcessorCount;
+    ctx->ccMajor = prop.major; ctx->ccMinor = prop.minor;
+    if ((e = cudaSetDevice(device)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->warpCounter, 64)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->statsDev, 8 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->aabbDev, 8 * sizeof(float))) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->countDev, sizeof(long long))) != cudaSuccess ||
+        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
+        setError(nullptr, B2RT_ERR_CUDA, "b2rt_create: %s", cudaGetErrorString(e));
+        b2rt_destroy(ctx);
+        return B2RT_ERR_CUDA;
+    }
+    cudaMemset(ctx->statsDev, 0, 8 * sizeof(unsigned long long));
+    *out = ctx;
+    return B2RT_OK;
+}
+
+void b2rt_destroy(b2rt_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->nodes); cudaFree(ctx->woop); cudaFree(ctx->triIndex);
+    cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch); cudaFree(ctx->stage);
+    cudaFree(ctx->aabbDev); cudaFree(ctx->countDev);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    delete ctx;
+}
+
+const char* b2rt_last_error(const b2rt_ctx* ctx) { return ctx ? ctx->lastError.c_str() : g_createError.c_str(); }
+int64_t b2rt_launch_count(const b2rt_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int b2rt_set_trace_config(b2rt_ctx* ctx, const b2rt_trace_config* cfg)
+{
+    if (!ctx || !cfg) return setError(ctx, B2RT_ERR_ARG, "b2rt_set_trace_config: NULL argument");
+    ctx->cfg = *cfg;
+    return B2RT_OK;
+}
+
+int b2rt_device_info(const b2rt_ctx* ctx, int* sm, int* major, int* minor)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (sm) *sm = ctx->smCount;
+    if (major) *major = ctx->ccMajor;
+    if (minor) *minor = ctx->ccMinor;
+    return B2RT_OK;
+}
+
+int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void* woop, size_t woopBytes,
+                 const int32_t* triIndex, size_t triIndexBytes, int layout, int srcIsDevice)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (layout != B2RT_LAYOUT_COMPACT2) return setError(ctx, B2RT_ERR_LAYOUT, "CudaTracer: Incorrect BVH layout!");
+    if (!nodes || !woop || !triIndex || nodeBytes < 64 || nodeBytes % 64 || woopBytes % 16 ||
+        triIndexBytes * 4 != woopBytes)
+        return setError(ctx, B2RT_ERR_ARG, "b2rt_set_bvh: inconsistent array sizes (nodes %zu, woop %zu, triIndex %zu)",
+                        nodeBytes, woopBytes, triIndexBytes);
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaFree(ctx->nodes); cudaFree(ctx->woop); cudaFree(ctx->triIndex);
+    ctx->nodes = nullptr; ctx->woop = nullptr; ctx->triIndex = nullptr; ctx->hasBvh = false;
+
+    // nodes: host round trip for the re-layout (one-off, at most tens of MB)
+    std::vector<float> in(nodeBytes / 4), out;
+    B2RT_CUDA(ctx, cudaMemcpy(in.data(), nodes, nodeBytes, srcIsDevice ? cudaMemcpyDeviceToHost : cudaMemcpyHostToHost));
+    int topCount = 0;
+    relayoutNodes(in, out, topCount);
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->nodes, nodeBytes));
+    B2RT_CUDA(ctx, cudaMemcpy(ctx->nodes, out.data(), nodeBytes, cudaMemcpyHostToDevice));
+    // Woop rows: the leaf loop fetches three rows before it looks at the terminator, so the copy
+    // carries two rows of padding past the last terminator (the reference relies on texture
+    // fetches returning zero out of range, kepler_dynamic_fetch.cu:328-334).
+    const cudaMemcpyKind kind = srcIsDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->woop, woopBytes + 32));
+    B2RT_CUDA(ctx, cudaMemset(reinterpret_cast<char*>(ctx->woop) + woopBytes, 0, 32));
+    if (woopBytes) B2RT_CUDA(ctx, cudaMemcpy(ctx->woop, woop, woopBytes, kind));
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->triIndex, triIndexBytes + 16));
+    if (triIndexBytes) B2RT_CUDA(ctx, cudaMemcpy(ctx->triIndex, triIndex, triIndexBytes, kind));
+    ctx->nodeBytes = nodeBytes; ctx->woopBytes = woopBytes; ctx->triIndexBytes = triIndexBytes;
+    ctx->topNodesAvail = topCount;
+    ctx->hasBvh = true;
+    return B2RT_OK;
+}
+
+int b2rt_get_bvh(const b2rt_ctx* ctx, const void** nodes, size_t* nodeBytes, const void** woop, size_t* woopBytes,
+                 const int32_t** triIndex, size_t* triIndexBytes)
+{
+    if (!ctx || !ctx->hasBvh) return B2RT_ERR_NO_BVH;
+    if (nodes) *nodes = ctx->nodes;
+    if (nodeBytes) *nodeBytes = ctx->nodeBytes;
+    if (woop) *woop = ctx->woop;
+    if (woopBytes) *woopBytes = ctx->woopBytes;
+    if (triIndex) *triIndex = ctx->triIndex;
+    if (triIndexBytes) *triIndexBytes = ctx->triIndexBytes;
+    return B2RT_OK;
+}
+
+int b2rt_trace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, void* stream, float* ms)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (ms) *ms = 0.0f;
+    if (numRays == 0) return B2RT_OK;                                   // CudaTracer.cc:123-125
+    if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
+    if (numRays < 0 || numRays > 0x7fffffff || !rays || !results)
+        return setError(ctx, B2RT_ERR_ARG, "b2rt_trace: bad ray buffer (n=%lld)", (long long)numRays);
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (ms) B2RT_CUDA(ctx, cudaEventRecord(ctx->ev0, s));
+    int rc = launchTrace(ctx, rays, results, numRays, flags, s);
+    if (rc) return rc;
+    if (ms) {
+        B2RT_CUDA(ctx, cudaEventRecord(ctx->ev1, s));
+        B2RT_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+        B2RT_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    }
+    return B2RT_OK;
+}
+
+int b2rt_trace_host(b2rt_ctx* ctx, const void* raysHost, void* resultsHost, int64_t numRays, unsigned flags,
+                    float* msKernel, float* msTotal)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (msKernel) *msKernel = 0.0f;
+    if (msTotal) *msTotal = 0.0f;
+    if (numRays == 0) return B2RT_OK;
+    if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
+    if (numRays < 0 || numRays > 0x7fffffff || !raysHost || !resultsHost)
+        return setError(ctx, B2RT_ERR_ARG, "b2rt_trace_host: bad ray buffer (n=%lld)", (long long)numRays);
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t rayBytes = (size_t)numRays * sizeof(Ray), resBytes = (size_t)numRays * sizeof(RayResult);
+    int rc = ensureStage(ctx, rayBytes + resBytes);
+    if (rc) return rc;
+    char* dRays = static_cast<char*>(ctx->stage);
+    char* dRes = dRays + rayBytes;
+    cudaEvent_t t0, t1;
+    B2RT_CUDA(ctx, cudaEventCreate(&t0));
+    B2RT_CUDA(ctx, cudaEventCreate(&t1));
+    cudaEventRecord(t0, 0);
+    cudaError_t e = cudaMemcpyAsync(dRays, raysHost, rayBytes, cudaMemcpyHostToDevice, 0);
+    // the kernel writes only id and t without WRITE_BARY (as CudaTracerKernels.hh:197): the pad
+    // words that travel back to the host are zero, not stale staging memory
+    if (e == cudaSuccess && !(flags & (B2RT_TRACE_WRITE_BARY | B2RT_TRACE_STATS)))
+        e = cudaMemsetAsync(dRes, 0, resBytes, 0);
+    if (e == cudaSuccess) e = cudaEventRecord(ctx->ev0, 0);
+    if (e == cudaSuccess) { rc = launchTrace(ctx, dRays, dRes, numRays, flags, 0); }
+    if (e == cudaSuccess && rc == 0) e = cudaEventRecord(ctx->ev1, 0);
+    if (e == cudaSuccess && rc == 0) e = cudaMemcpyAsync(resultsHost, dRes, resBytes, cudaMemcpyDeviceToHost, 0);
+    if (e == cudaSuccess && rc == 0) e = cudaEventRecord(t1, 0);
+    if (e == cudaSuccess && rc == 0) e = cudaEventSynchronize(t1);
+    if (e == cudaSuccess && rc == 0) {
+        if (msKernel) cudaEventElapsedTime(msKernel, ctx->ev0, ctx->ev1);
+        if (msTotal) cudaEventElapsedTime(msTotal, t0, t1);
+    }
+    cudaEventDestroy(t0); cudaEventDestroy(t1);
+    if (rc) return rc;
+    if (e != cudaSuccess) return setError(ctx, B2RT_ERR_CUDA, "b2rt_trace_host: %s", cudaGetErrorString(e));
+    return B2RT_OK;
+}
+
+int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out)
+{
+    if (!ctx || !out) return B2RT_ERR_ARG;
+    unsigned long long h[8];
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2RT_CUDA(ctx, cudaDeviceSynchronize());
+    B2RT_CUDA(ctx, cudaMemcpy(h, ctx->statsDev, sizeof(h), cudaMemcpyDeviceToHost));
+    out->node_iters = h[0]; out->node_lanes = h[1]; out->tri_iters = h[2]; out->tri_lanes = h[3];
+    out->fetches = h[4]; out->rays = h[5];
+    return B2RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,107 @@
+// common.cuh -- shared declarations of libb2rt (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+
+#include "../../include/b2rt.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libb2rt is written for sm_100a (B200) only"
+#endif
+
+namespace b2rt {
+
+// rt/Util.hh:64-89 -- record layouts (ABI)
+struct Ray       { float ox, oy, oz, tmin, dx, dy, dz, tmax; };
+struct RayResult { int32_t id; float t; int32_t padA, padB; };
+struct MortonKey { int32_t oldSlot; uint32_t hash[6]; };       // ray/RayBufferKernels.hh:46-50
+static_assert(sizeof(Ray) == 32 && sizeof(RayResult) == 16 && sizeof(MortonKey) == 28, "ABI");
+
+constexpr int kSentinel = B2RT_ENTRYPOINT_SENTINEL;
+
+}  // namespace b2rt
+
+// One context per device.  Owns the private BVH copy, the persistent-thread work counter,
+// scratch for the sort and the event pair used when the caller asks for kernel milliseconds.
+struct b2rt_ctx {
+    int device = 0;
+    int smCount = 0, ccMajor = 0, ccMinor = 0;
+    std::string lastError;
+    int64_t launches = 0;
+
+    // private BVH copy (nodes re-laid: top levels first)
+    float4* nodes = nullptr;   size_t nodeBytes = 0;
+    float4* woop = nullptr;    size_t woopBytes = 0;
+    int32_t* triIndex = nullptr; size_t triIndexBytes = 0;
+    int topNodesAvail = 0;     // how many leading nodes are in breadth-first order
+    bool hasBvh = false;
+
+    b2rt_trace_config cfg = { -1, -1, -1, 0 };
+
+    int* warpCounter = nullptr;                 // work counter for persistent warps
+    unsigned long long* statsDev = nullptr;     // 8 counters for the instrumented kernel
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    // scratch (grown on demand, never shrunk)
+    void* scratch = nullptr;  size_t scratchBytes = 0;
+    void* stage = nullptr;    size_t stageBytes = 0;   // device staging for b2rt_trace_host
+    float* aabbDev = nullptr;                   // 6 floats
+    long long* countDev = nullptr;              // hit counter
+};
+
+namespace b2rt {
+
+int setError(b2rt_ctx* ctx, int code, const char* fmt, ...);
+int ensureScratch(b2rt_ctx* ctx, size_t bytes);
+extern std::string g_createError;
+
+#define B2RT_CUDA(ctx, call)                                                                   \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess)                                                                 \
+            return b2rt::setError((ctx), B2RT_ERR_CUDA, "%s failed: %s (%s:%d)", #call,        \
+                                  cudaGetErrorString(e_), __FILE__, __LINE__);                 \
+    } while (0)
+
+#define B2RT_CHECK_LAUNCH(ctx, name)                                                           \
+    do {                                                                                       \
+        cudaError_t e_ = cudaGetLastError();                                                   \
+        if (e_ != cudaSuccess)                                                                 \
+            return b2rt::setError((ctx), B2RT_ERR_CUDA, "launch of %s failed: %s", name,       \
+                                  cudaGetErrorString(e_));                                     \
+        (ctx)->launches++;                                                                     \
+    } while (0)
+
+// kernels' launchers (defined in the .cu files)
+int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
+                cudaStream_t stream);
+
+// device helpers
+#ifdef __CUDACC__
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+__device__ __forceinline__ float rcp_approx(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// sm_100a three-input float min/max (SASS FMNMX3)
+__device__ __forceinline__ float fmin3(float a, float b, float c)
+{
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c)
+{
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+#endif
+
+}  // namespace b2rt

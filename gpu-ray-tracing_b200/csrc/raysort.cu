@@ -1,0 +1,430 @@
+// raysort.cu -- Morton-code ray sort, entirely on the device.
+//
+// Replaces RayBuffer::mortonSort (ray/RayBuffer.cc:256-324), findAABBKernel /
+// genMortonKeysKernel / reorderRaysKernel (ray/RayBufferKernels.cu:74-200) and, above all, the
+// D2H copy -> single-thread CPU quicksort -> H2D copy in the middle of it (RayBuffer.cc:291-297,
+// framework/base/Sort.cc:131-165).
+//
+//  1. AABB of ray origins and end points: grid-stride loop, warp shuffles, one ordered-uint
+//     atomicMin/Max per block (the reference reduces through shared memory without __syncwarp
+//     and finishes with a float CAS loop, RayBufferKernels.cu:38-62,108-113).
+//  2. 192-bit key: bit i of component c lands at key bit 6i + c (collectBits, :66-70); done with
+//     compile-time shifts in registers, no shared-memory read-modify-writes.  Stored as three
+//     64-bit words (lo/mid/hi) for the sort and, for b2rt_morton_keys, as the reference's 28-byte
+//     MortonKey records.
+//  3. Stable LSD radix sort, 8 bits per pass, over the 192-bit key carried as (64-bit word,
+//     32-bit slot) pairs: 8 passes on the low word, gather the middle word, 8 passes, gather the
+//     high word, and as many passes as it has significant bits (keys of in-range rays end at bit
+//     155).  Each pass = block histograms, one scan kernel (one CTA per bin), a stable scatter
+//     that ranks with __match_any_sync -- no atomics on the data path.
+//  4. Gather of rays by sorted slot + rebuild of idToSlot / slotToID (reorderRaysKernel).
+// Compiled with -fmad=false so the quantised components are bit-identical to the CPU oracle.
+#include "common.cuh"
+
+namespace b2rt {
+
+typedef unsigned long long u64;
+
+__device__ __forceinline__ unsigned orderedBits(float f)
+{
+    const unsigned b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float orderedToFloat(unsigned u)
+{
+    const unsigned b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+}
+
+__global__ void aabbInitKernel(unsigned* box)
+{
+    if (threadIdx.x < 3) box[threadIdx.x] = 0xffffffffu;        // lo: identity of min
+    else if (threadIdx.x < 6) box[threadIdx.x] = 0u;            // hi: identity of max
+}
+
+__global__ void __launch_bounds__(256) findAABBKernel(const float4* __restrict__ rays, int n, unsigned* box)
+{
+    const float big = 3.402823466e+38f;
+    float lo[3] = { big, big, big }, hi[3] = { -big, -big, -big };
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float4 o = __ldg(rays + 2 * i), d = __ldg(rays + 2 * i + 1);
+        const float e[3] = { o.x + d.x * d.w, o.y + d.y * d.w, o.z + d.z * d.w };
+        const float oo[3] = { o.x, o.y, o.z };
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            lo[k] = fminf(fminf(lo[k], oo[k]), e[k]);
+            hi[k] = fmaxf(fmaxf(hi[k], oo[k]), e[k]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+        for (int s = 16; s > 0; s >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], s));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], s));
+        }
+    __shared__ float s_lo[8][3], s_hi[8][3];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0)
+        for (int k = 0; k < 3; k++) { s_lo[warp][k] = lo[k]; s_hi[warp][k] = hi[k]; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        const int k = threadIdx.x;
+        float a = s_lo[0][k], b = s_hi[0][k];
+        for (int w = 1; w < (int)(blockDim.x >> 5); w++) { a = fminf(a, s_lo[w][k]); b = fmaxf(b, s_hi[w][k]); }
+        atomicMin(box + k, orderedBits(a));
+        atomicMax(box + 3 + k, orderedBits(b));
+    }
+}
+
+// hash[(6i+c) >> 5] |= bit i of v << ((6i+c) & 31), for i = 0..31 -- all shifts are constants
+template <int C>
+__device__ __forceinline__ void scatterBits(unsigned (&hash)[6], unsigned v)
+{
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        const int pos = 6 * i + C, w = pos >> 5, sh = pos & 31;
+        const unsigned moved = (sh >= i) ? (v << (sh - i)) : (v >> (i - sh));
+        hash[w] |= moved & (1u << sh);
+    }
+}
+
+// box: ordered-uint AABB (device) ; boxF: optional float AABB (for b2rt_morton_keys)
+template <bool AOS>
+__global__ void __launch_bounds__(256) mortonKeysKernel(const float4* __restrict__ rays, int n, const unsigned* box,
+                                                        const float* boxF, u64* lo, u64* mid, u64* hi,
+                                                        unsigned* slots, MortonKey* keysAos)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float bl[3], bh[3];
+    if (boxF) { for (int k = 0; k < 3; k++) { bl[k] = boxF[k]; bh[k] = boxF[3 + k]; } }
+    else      { for (int k = 0; k < 3; k++) { bl[k] = orderedToFloat(box[k]); bh[k] = orderedToFloat(box[3 + k]); } }
+    const float4 o = __ldg(rays + 2 * (size_t)i), d = __ldg(rays + 2 * (size_t)i + 1);
+    const float ax = (o.x - bl[0]) / (bh[0] - bl[0]);
+    const float ay = (o.y - bl[1]) / (bh[1] - bl[1]);
+    const float az = (o.z - bl[2]) / (bh[2] - bl[2]);
+    float l = 0.0f;
+    l += d.x * d.x; l += d.y * d.y; l += d.z * d.z;
+    const float len = sqrtf(l);
+    const float s = 1.0f * ((len != 0.0f) ? 1.0f / len : 0.0f);
+    const float bx = (d.x * s + 1.0f) * 0.5f, by = (d.y * s + 1.0f) * 0.5f, bz = (d.z * s + 1.0f) * 0.5f;
+    unsigned hash[6] = { 0, 0, 0, 0, 0, 0 };
+    // (U32)f on the device saturates: NaN and negatives -> 0, too large -> 0xffffffff
+    scatterBits<0>(hash, __float2uint_rz(ax * 256.0f * 65536.0f));
+    scatterBits<1>(hash, __float2uint_rz(ay * 256.0f * 65536.0f));
+    scatterBits<2>(hash, __float2uint_rz(az * 256.0f * 65536.0f));
+    scatterBits<3>(hash, __float2uint_rz(bx * 32.0f * 65536.0f));
+    scatterBits<4>(hash, __float2uint_rz(by * 32.0f * 65536.0f));
+    scatterBits<5>(hash, __float2uint_rz(bz * 32.0f * 65536.0f));
+    if (AOS) {
+        MortonKey k;
+        k.oldSlot = i;
+        for (int j = 0; j < 6; j++) k.hash[j] = hash[j];
+        keysAos[i] = k;
+    } else {
+        lo[i] = (u64)hash[0] | ((u64)hash[1] << 32);
+        mid[i] = (u64)hash[2] | ((u64)hash[3] << 32);
+        hi[i] = (u64)hash[4] | ((u64)hash[5] << 32);
+        slots[i] = (unsigned)i;
+    }
+}
+
+// ---- radix sort ------------------------------------------------------------------------------
+constexpr int kRsThreads = 256, kRsItems = 16, kRsTile = kRsThreads * kRsItems, kRsBins = 256;
+constexpr int kRsWarps = kRsThreads / 32, kRsWarpTile = kRsTile / kRsWarps;
+
+// blockHist layout: [bin][block]
+__global__ void __launch_bounds__(kRsThreads) rsHistKernel(const u64* __restrict__ keys, int n, int shift,
+                                                           unsigned* blockHist, int numBlocks, u64* orReduce)
+{
+    __shared__ unsigned hist[kRsBins];
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    const long long base = (long long)blockIdx.x * kRsTile;
+    u64 ored = 0;
+#pragma unroll 4
+    for (int j = 0; j < kRsItems; j++) {
+        const long long i = base + j * kRsThreads + threadIdx.x;
+        if (i < n) {
+            const u64 k = keys[i];
+            ored |= k;
+            atomicAdd(&hist[(unsigned)(k >> shift) & 0xffu], 1u);
+        }
+    }
+    __syncthreads();
+    blockHist[(size_t)threadIdx.x * numBlocks + blockIdx.x] = hist[threadIdx.x];
+    if (orReduce) {     // OR of all keys of this word: tells the host-free pass loop which digits are all zero
+        for (int s = 16; s > 0; s >>= 1) ored |= __shfl_xor_sync(0xffffffffu, ored, s);
+        if ((threadIdx.x & 31) == 0 && ored) atomicOr(orReduce, ored);
+    }
+}
+
+// one CTA per bin: exclusive scan of that bin's row, total to binTotal[bin]
+__global__ void __launch_bounds__(512) rsScanKernel(unsigned* blockHist, int numBlocks, unsigned* binTotal)
+{
+    __shared__ unsigned warpSum[16];
+    __shared__ unsigned carry;
+    unsigned* row = blockHist + (size_t)blockIdx.x * numBlocks;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < numBlocks; base += 512) {
+        const int i = base + threadIdx.x;
+        const unsigned v = (i < numBlocks) ? row[i] : 0u;
+        unsigned incl = v;
+        for (int s = 1; s < 32; s <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += t; }
+        if (lane == 31) warpSum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned w = (lane < 16) ? warpSum[lane] : 0u;
+            for (int s = 1; s < 16; s <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, w, s); if (lane >= s) w += t; }
+            if (lane < 16) warpSum[lane] = w;       // inclusive over warps
+        }
+        __syncthreads();
+        const unsigned warpBase = (warp == 0) ? 0u : warpSum[warp - 1];
+        const unsigned c = carry;
+        if (i < numBlocks) row[i] = c + warpBase + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = c + warpSum[15];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) binTotal[blockIdx.x] = carry;
+}
+
+__global__ void __launch_bounds__(kRsThreads) rsScatterKernel(const u64* __restrict__ keysIn, const unsigned* __restrict__ slotsIn,
+                                                              u64* keysOut, unsigned* slotsOut, int n, int shift,
+                                                              const unsigned* __restrict__ blockHist, int numBlocks,
+                                                              const unsigned* __restrict__ binTotal)
+{
+    __shared__ unsigned warpHist[kRsWarps][kRsBins];
+    __shared__ unsigned binBase[kRsBins];
+    __shared__ unsigned scanTmp[kRsWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int w = 0; w < kRsWarps; w++) warpHist[w][threadIdx.x] = 0;
+    // exclusive scan of the 256 bin totals
+    {
+        const unsigned v = binTotal[threadIdx.x];
+        unsigned incl = v;
+        for (int s = 1; s < 32; s <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += t; }
+        if (lane == 31) scanTmp[warp] = incl;
+        __syncthreads();
+        unsigned wb = 0;
+        for (int w = 0; w < warp; w++) wb += scanTmp[w];
+        binBase[threadIdx.x] = wb + incl - v;
+    }
+    __syncthreads();
+
+    const long long warpBase = (long long)blockIdx.x * kRsTile + (long long)warp * kRsWarpTile;
+    u64 key[kRsItems];
+    unsigned digit[kRsItems];
+    // phase A: per-warp digit counts, in element order
+#pragma unroll
+    for (int j = 0; j < kRsItems; j++) {
+        const long long i = warpBase + j * 32 + lane;
+        const bool valid = i < n;
+        key[j] = valid ? keysIn[i] : 0ull;
+        digit[j] = valid ? ((unsigned)(key[j] >> shift) & 0xffu) : 0xffffffffu;
+        const unsigned peers = __match_any_sync(0xffffffffu, digit[j]);
+        if (valid && lane == __ffs(peers) - 1) warpHist[warp][digit[j]] += __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    // phase B: turn counts into destinations: global base of (bin, block) + earlier warps of this block
+    {
+        const int bin = threadIdx.x;
+        unsigned running = binBase[bin] + blockHist[(size_t)bin * numBlocks + blockIdx.x];
+        for (int w = 0; w < kRsWarps; w++) { const unsigned c = warpHist[w][bin]; warpHist[w][bin] = running; running += c; }
+    }
+    __syncthreads();
+    // phase C: stable scatter
+#pragma unroll
+    for (int j = 0; j < kRsItems; j++) {
+        const long long i = warpBase + j * 32 + lane;
+        const bool valid = i < n;
+        const unsigned peers = __match_any_sync(0xffffffffu, digit[j]);
+        unsigned dst = 0;
+        if (valid) {
+            dst = warpHist[warp][digit[j]] + __popc(peers & ((1u << lane) - 1u));
+            keysOut[dst] = key[j];
+            slotsOut[dst] = slotsIn[i];
+        }
+        __syncwarp();
+        if (valid && lane == __ffs(peers) - 1) warpHist[warp][digit[j]] += __popc(peers);
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(256) gatherWordKernel(const u64* __restrict__ word, const unsigned* __restrict__ slots, u64* out, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = word[slots[i]];
+}
+
+// reorderRaysKernel -- RayBufferKernels.cu:183-200
+__global__ void __launch_bounds__(256) reorderRaysKernel(const unsigned* __restrict__ sortedSlots, const float4* __restrict__ inRays,
+                                                         const int32_t* __restrict__ inSlotToID, float4* outRays,
+                                                         int32_t* outIDToSlot, int32_t* outSlotToID, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned oldSlot = sortedSlots[i];
+    const int id = inSlotToID[oldSlot];
+    outRays[2 * (size_t)i] = __ldg(inRays + 2 * (size_t)oldSlot);
+    outRays[2 * (size_t)i + 1] = __ldg(inRays + 2 * (size_t)oldSlot + 1);
+    outIDToSlot[id] = i;
+    outSlotToID[i] = id;
+}
+
+static inline size_t alignUp(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static int findAABB(b2rt_ctx* ctx, const void* rays, int n, cudaStream_t s)
+{
+    unsigned* box = reinterpret_cast<unsigned*>(ctx->aabbDev);
+    aabbInitKernel<<<1, 32, 0, s>>>(box);
+    B2RT_CHECK_LAUNCH(ctx, "aabbInitKernel");
+    int grid = (n + 255) / 256;
+    const int cap = ctx->smCount * 8;
+    if (grid > cap) grid = cap;
+    findAABBKernel<<<grid, 256, 0, s>>>(static_cast<const float4*>(rays), n, box);
+    B2RT_CHECK_LAUNCH(ctx, "findAABBKernel");
+    return B2RT_OK;
+}
+
+static int readAABB(b2rt_ctx* ctx, float out[6], cudaStream_t s)
+{
+    unsigned h[6];
+    B2RT_CUDA(ctx, cudaMemcpyAsync(h, ctx->aabbDev, sizeof(h), cudaMemcpyDeviceToHost, s));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(s));
+    for (int k = 0; k < 6; k++) out[k] = orderedToFloat(h[k]);
+    return B2RT_OK;
+}
+
+}  // namespace b2rt
+
+using namespace b2rt;
+
+extern "C" {
+
+int b2rt_find_aabb(b2rt_ctx* ctx, const void* rays, int64_t n, float aabbOut[6], void* stream)
+{
+    if (!ctx || !aabbOut) return B2RT_ERR_ARG;
+    if (n < 0 || n > 0x7fffffff || (n && !rays)) return setError(ctx, B2RT_ERR_ARG, "b2rt_find_aabb: bad arguments");
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = findAABB(ctx, rays, (int)n, s);
+    if (rc) return rc;
+    return readAABB(ctx, aabbOut, s);
+}
+
+int b2rt_morton_keys(b2rt_ctx* ctx, const void* rays, int64_t n, const float aabb[6], void* keys, void* stream)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (n < 0 || n > 0x7fffffff || !aabb || (n && (!rays || !keys))) return setError(ctx, B2RT_ERR_ARG, "b2rt_morton_keys: bad arguments");
+    if (n == 0) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    float* boxF = ctx->aabbDev;     // 8 floats allocated; reuse as float box
+    B2RT_CUDA(ctx, cudaMemcpyAsync(boxF, aabb, 6 * sizeof(float), cudaMemcpyHostToDevice, s));
+    mortonKeysKernel<true><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(static_cast<const float4*>(rays), (int)n, nullptr, boxF,
+                                                                      nullptr, nullptr, nullptr, nullptr, static_cast<MortonKey*>(keys));
+    B2RT_CHECK_LAUNCH(ctx, "mortonKeysKernel");
+    B2RT_CUDA(ctx, cudaStreamSynchronize(s));   // aabb is a host pointer the caller may reuse
+    return B2RT_OK;
+}
+
+int b2rt_morton_sort(b2rt_ctx* ctx, void* rays, int32_t* idToSlot, int32_t* slotToID, int64_t n64, float aabbOut[6], void* stream)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (n64 < 0 || n64 > 0x7fffffff || (n64 && (!rays || !idToSlot || !slotToID)))
+        return setError(ctx, B2RT_ERR_ARG, "b2rt_morton_sort: bad arguments");
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int n = (int)n64;
+    if (n == 0) {
+        if (aabbOut) { for (int k = 0; k < 3; k++) { aabbOut[k] = 3.402823466e+38f; aabbOut[3 + k] = -3.402823466e+38f; } }
+        return B2RT_OK;
+    }
+    const int numBlocks = (n + kRsTile - 1) / kRsTile;
+    // scratch layout
+    const size_t wordB = alignUp((size_t)n * 8), slotB = alignUp((size_t)n * 4);
+    const size_t histB = alignUp((size_t)kRsBins * numBlocks * 4);
+    const size_t rayB = alignUp((size_t)n * 32);
+    size_t total = 3 * wordB + 2 * wordB + 2 * slotB + histB + 4096 + rayB + slotB;
+    int rc = ensureScratch(ctx, total);
+    if (rc) return rc;
+    char* base = static_cast<char*>(ctx->scratch);
+    u64* wLo = reinterpret_cast<u64*>(base); base += wordB;
+    u64* wMid = reinterpret_cast<u64*>(base); base += wordB;
+    u64* wHi = reinterpret_cast<u64*>(base); base += wordB;
+    u64* kA = reinterpret_cast<u64*>(base); base += wordB;
+    u64* kB = reinterpret_cast<u64*>(base); base += wordB;
+    unsigned* sA = reinterpret_cast<unsigned*>(base); base += slotB;
+    unsigned* sB = reinterpret_cast<unsigned*>(base); base += slotB;
+    unsigned* blockHist = reinterpret_cast<unsigned*>(base); base += histB;
+    unsigned* binTotal = reinterpret_cast<unsigned*>(base);
+    u64* orWord = reinterpret_cast<u64*>(base + 2048); base += 4096;
+    float4* oldRays = reinterpret_cast<float4*>(base); base += rayB;
+    int32_t* oldSlotToID = reinterpret_cast<int32_t*>(base);
+
+    rc = findAABB(ctx, rays, n, s);
+    if (rc) return rc;
+    const unsigned g = (unsigned)((n + 255) / 256);
+    mortonKeysKernel<false><<<g, 256, 0, s>>>(static_cast<const float4*>(rays), n, reinterpret_cast<unsigned*>(ctx->aabbDev), nullptr,
+                                             wLo, wMid, wHi, sA, nullptr);
+    B2RT_CHECK_LAUNCH(ctx, "mortonKeysKernel");
+
+    // Keys of rays inside the AABB end at bit 155 (24+1 bits x 3 at stride 6, components 0-2), so
+    // the high word normally needs 4 passes; out-of-range input (NaN boxes etc.) may set more
+    // bits, so the pass count for each word comes from an OR-reduction of that word.
+    unsigned* slotsCur = sA; unsigned* slotsAlt = sB;
+    const u64* words[3] = { wLo, wMid, wHi };
+    for (int w = 0; w < 3; w++) {
+        const u64* cur;
+        if (w == 0) cur = wLo;
+        else {
+            gatherWordKernel<<<g, 256, 0, s>>>(words[w], slotsCur, kA, n);
+            B2RT_CHECK_LAUNCH(ctx, "gatherWordKernel");
+            cur = kA;
+        }
+        u64* outBuf = (cur == kA) ? kB : kA;
+        int passes = 8;
+        if (w == 2) {
+            // OR-reduce the high word to find its highest significant byte
+            B2RT_CUDA(ctx, cudaMemsetAsync(orWord, 0, 8, s));
+            rsHistKernel<<<numBlocks, kRsThreads, 0, s>>>(cur, n, 0, blockHist, numBlocks, orWord);
+            B2RT_CHECK_LAUNCH(ctx, "rsHistKernel");
+            u64 h = 0;
+            B2RT_CUDA(ctx, cudaMemcpyAsync(&h, orWord, 8, cudaMemcpyDeviceToHost, s));
+            B2RT_CUDA(ctx, cudaStreamSynchronize(s));
+            passes = 0;
+            while (h) { passes++; h >>= 8; }
+        }
+        for (int pass = 0; pass < passes; pass++) {
+            const int shift = pass * 8;
+            if (!(w == 2 && pass == 0)) {       // the w == 2 first histogram was taken above
+                rsHistKernel<<<numBlocks, kRsThreads, 0, s>>>(cur, n, shift, blockHist, numBlocks, nullptr);
+                B2RT_CHECK_LAUNCH(ctx, "rsHistKernel");
+            }
+            rsScanKernel<<<kRsBins, 512, 0, s>>>(blockHist, numBlocks, binTotal);
+            B2RT_CHECK_LAUNCH(ctx, "rsScanKernel");
+            rsScatterKernel<<<numBlocks, kRsThreads, 0, s>>>(cur, slotsCur, outBuf, slotsAlt, n, shift, blockHist, numBlocks, binTotal);
+            B2RT_CHECK_LAUNCH(ctx, "rsScatterKernel");
+            const u64* done = outBuf;
+            outBuf = (done == kA) ? kB : kA;
+            // `cur` may be wLo on the very first pass; afterwards it ping-pongs between kA and kB
+            cur = done;
+            unsigned* t = slotsCur; slotsCur = slotsAlt; slotsAlt = t;
+        }
+    }
+
+    B2RT_CUDA(ctx, cudaMemcpyAsync(oldRays, rays, (size_t)n * 32, cudaMemcpyDeviceToDevice, s));
+    B2RT_CUDA(ctx, cudaMemcpyAsync(oldSlotToID, slotToID, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    reorderRaysKernel<<<g, 256, 0, s>>>(slotsCur, oldRays, oldSlotToID, static_cast<float4*>(rays), idToSlot, slotToID, n);
+    B2RT_CHECK_LAUNCH(ctx, "reorderRaysKernel");
+    if (aabbOut) return readAABB(ctx, aabbOut, s);
+    return B2RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,292 @@
+// trace.cu -- the hot path: batched closest-hit / any-hit traversal of a Compact2 BVH.
+//
+// Replaces rt/kernels/kepler_dynamic_fetch.cu:66-411 (`trace`) and its launcher :432-474.
+// Written from scratch for sm_100a; what it shares with the reference is the contract
+// (record layouts, child encoding, leaf terminator, result semantics), not the code:
+//
+//  * persistent warps pull rays through one global counter; the refill is aggregated per warp
+//    with __ballot_sync/__popc/__shfl_sync (no shared-memory mailbox, no volatile), and every
+//    lane stays in the loop until the whole warp is out of work, so all votes use a full mask;
+//  * while-while traversal with one postponed leaf (speculative traversal) and a dynamic
+//    refill when fewer than `fetchThreshold` lanes are still traversing;
+//  * nodes (64 B) and Woop triangles (48 B) are read with 128-bit loads; the first `topF4/4`
+//    nodes of the re-laid node array (breadth-first top of the tree) are staged in shared
+//    memory once per CTA and read from there;
+//  * the traversal stack keeps its top entry in a register, the next STACK_SMEM entries in
+//    shared memory (bank = lane, conflict free) and spills the rest to local memory;
+//  * slab test with 3-input FMNMX3 min/max, Woop test with explicit FMA order and
+//    rcp.approx (the reference is built with --use_fast_math, Makefile:120);
+//  * a result is stored exactly once per ray (the reference re-stores partial results at every
+//    dynamic-fetch exit, kepler_dynamic_fetch.cu:400-408), 16 B with barycentrics or 8 B without.
+#include "common.cuh"
+
+namespace b2rt {
+
+struct TraceParams {
+    const float4* __restrict__ rays;
+    int4* __restrict__ results;
+    const float4* __restrict__ nodes;
+    const float4* __restrict__ woop;
+    const int* __restrict__ triIndex;
+    int numRays;
+    int topF4;              // float4 elements of the node array staged in shared memory
+    int fetchThreshold;
+    int* warpCounter;
+    unsigned long long* stats;
+};
+
+constexpr int kLocalStack = 64;     // SplitBVHBuilder MaxDepth = 64 bounds the stack (SplitBVHBuilder.hh:43)
+constexpr unsigned kFull = 0xffffffffu;
+
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS>
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
+{
+    extern __shared__ float4 s_dyn[];
+    float4* s_top = s_dyn;
+    int* s_stack = reinterpret_cast<int*>(s_dyn + p.topF4) + threadIdx.x;   // slot k at s_stack[k * BLOCK]
+
+    // Stage the top of the tree (same bytes for every CTA; L2 serves all but the first).
+    for (int i = threadIdx.x; i < p.topF4; i += BLOCK) s_top[i] = ldg4(p.nodes + i);
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const int topF4 = p.topF4;
+    int lstack[kLocalStack];            // spill area, touched only when a stack outgrows STACK_SMEM
+
+    // Per-ray state.
+    float origx = 0, origy = 0, origz = 0, dirx = 0, diry = 0, dirz = 0;
+    float idirx = 0, idiry = 0, idirz = 0, oodx = 0, oody = 0, oodz = 0, tmin = 0, hitT = 0;
+    float hitU = 0, hitV = 0;
+    int hitIndex = -1, rayidx = -1;
+    int nodeAddr = kSentinel;           // >= 0 inner node, < 0 leaf, sentinel = finished
+    int leafAddr = 0;                   // postponed leaf (< 0) or none (>= 0)
+    int tos = kSentinel;                // top of stack, in a register
+    int sp = 0;                         // number of entries held in memory
+    bool poolEmpty = false;             // warp-uniform: the work counter ran past numRays
+
+    unsigned long long stNodeIters = 0, stNodeLanes = 0, stTriIters = 0, stTriLanes = 0, stFetches = 0;
+
+    auto stackStore = [&](int slot, int v) {
+        if (slot < STACK_SMEM) s_stack[slot * BLOCK] = v; else lstack[slot - STACK_SMEM] = v;
+    };
+    auto stackLoad = [&](int slot) -> int {
+        return (slot < STACK_SMEM) ? s_stack[slot * BLOCK] : lstack[slot - STACK_SMEM];
+    };
+    auto push = [&](int v) { stackStore(sp, tos); sp++; tos = v; };
+    auto pop = [&]() -> int { int r = tos; sp--; tos = stackLoad(sp); return r; };
+
+    while (true) {
+        __syncwarp();
+        // ---- store finished rays, refill -------------------------------------------------
+        const bool terminated = (nodeAddr == kSentinel);
+        if (terminated && rayidx >= 0) {
+            const int id = (hitIndex == -1) ? -1 : __ldg(p.triIndex + hitIndex);
+            if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
+            else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
+            rayidx = -1;
+        }
+        const unsigned maskT = __ballot_sync(kFull, terminated);
+        if (maskT != 0 && !poolEmpty) {
+            const int numT = __popc(maskT);
+            const int leader = __ffs(maskT) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(p.warpCounter, numT);
+            base = __shfl_sync(kFull, base, leader);
+            if (STATS && lane == leader) stFetches++;
+            poolEmpty = (base + numT >= p.numRays);
+            if (terminated) {
+                const int idx = base + __popc(maskT & ((1u << lane) - 1u));
+                if (idx < p.numRays) {
+                    rayidx = idx;
+                    const float4 o = ldg4(p.rays + 2 * (size_t)idx);
+                    const float4 d = ldg4(p.rays + 2 * (size_t)idx + 1);
+                    origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
+                    dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
+                    const float ooeps = 8.271806125530277e-25f;    // 2^-80, avoids division by zero
+                    idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+                    idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+                    idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+                    oodx = origx * idirx; oody = origy * idiry; oodz = origz * idirz;
+                    // stack: memory slot 0 and the register both hold the sentinel
+                    stackStore(0, kSentinel);
+                    sp = 1; tos = kSentinel;
+                    leafAddr = 0; nodeAddr = 0; hitIndex = -1;
+                }
+            }
+        }
+        if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break;     // warp out of work
+
+        const int threshold = poolEmpty ? 0 : p.fetchThreshold;
+
+        // ---- traversal --------------------------------------------------------------------
+        while (nodeAddr != kSentinel) {
+            // inner nodes, until every participating lane holds a postponed leaf
+            while ((unsigned)nodeAddr < (unsigned)kSentinel) {
+                if (STATS) { const unsigned am = __activemask(); stNodeLanes++; if (lane == __ffs(am) - 1) stNodeIters++; }
+                const float4* np = (nodeAddr < topF4) ? (s_top + nodeAddr) : (p.nodes + nodeAddr);
+                float4 n0xy, n1xy, nz, cn;
+                if (nodeAddr < topF4) { n0xy = np[0]; n1xy = np[1]; nz = np[2]; cn = np[3]; }
+                else { n0xy = ldg4(np); n1xy = ldg4(np + 1); nz = ldg4(np + 2); cn = ldg4(np + 3); }
+                int c0 = __float_as_int(cn.x), c1 = __float_as_int(cn.y);
+
+                const float c0lox = __fmaf_rn(n0xy.x, idirx, -oodx), c0hix = __fmaf_rn(n0xy.y, idirx, -oodx);
+                const float c0loy = __fmaf_rn(n0xy.z, idiry, -oody), c0hiy = __fmaf_rn(n0xy.w, idiry, -oody);
+                const float c0loz = __fmaf_rn(nz.x, idirz, -oodz),   c0hiz = __fmaf_rn(nz.y, idirz, -oodz);
+                const float c1loz = __fmaf_rn(nz.z, idirz, -oodz),   c1hiz = __fmaf_rn(nz.w, idirz, -oodz);
+                const float c1lox = __fmaf_rn(n1xy.x, idirx, -oodx), c1hix = __fmaf_rn(n1xy.y, idirx, -oodx);
+                const float c1loy = __fmaf_rn(n1xy.z, idiry, -oody), c1hiy = __fmaf_rn(n1xy.w, idiry, -oody);
+                const float c0min = fmax3(fminf(c0lox, c0hix), fminf(c0loy, c0hiy), fmaxf(fminf(c0loz, c0hiz), tmin));
+                const float c0max = fmin3(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy), fminf(fmaxf(c0loz, c0hiz), hitT));
+                const float c1min = fmax3(fminf(c1lox, c1hix), fminf(c1loy, c1hiy), fmaxf(fminf(c1loz, c1hiz), tmin));
+                const float c1max = fmin3(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy), fminf(fmaxf(c1loz, c1hiz), hitT));
+
+                const bool trav0 = (c0max >= c0min);
+                const bool trav1 = (c1max >= c1min);
+                if (!trav0 && !trav1) {
+                    nodeAddr = pop();
+                } else {
+                    nodeAddr = trav0 ? c0 : c1;
+                    if (trav0 && trav1) {
+                        if (c1min < c0min) { const int t = nodeAddr; nodeAddr = c1; c1 = t; }
+                        push(c1);
+                    }
+                }
+                // first leaf: postpone it and keep traversing
+                if (nodeAddr < 0 && leafAddr >= 0) {
+                    leafAddr = nodeAddr;
+                    nodeAddr = pop();
+                }
+                // every lane still here holds a leaf -> go intersect
+                if (!__any_sync(__activemask(), leafAddr >= 0)) break;
+            }
+
+            // postponed leaves
+            while (leafAddr < 0) {
+                for (int triAddr = ~leafAddr;; triAddr += 3) {
+                    const float4 v00 = ldg4(p.woop + triAddr);
+                    const float4 v11 = ldg4(p.woop + triAddr + 1);
+                    const float4 v22 = ldg4(p.woop + triAddr + 2);
+                    if (__float_as_int(v00.x) == (int)0x80000000) break;       // leaf terminator
+                    if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
+
+                    const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
+                    const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
+                    const float t = __fmul_rn(Oz, invDz);
+                    if (t > tmin && t < hitT) {
+                        const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
+                        const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
+                        const float u = __fmaf_rn(t, Dx, Ox);
+                        if (u >= 0.0f) {
+                            const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
+                            const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
+                            const float v = __fmaf_rn(t, Dy, Oy);
+                            if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                                hitT = t; hitIndex = triAddr;
+                                if (BARY) { hitU = u; hitV = v; }
+                                if (ANY_HIT) { nodeAddr = kSentinel; break; }
+                            }
+                        }
+                    }
+                }
+                // a second leaf may be sitting in nodeAddr
+                leafAddr = nodeAddr;
+                if (nodeAddr < 0) nodeAddr = pop();
+            }
+
+            // dynamic fetch: too few lanes left -> leave and refill the idle ones
+            if (__popc(__activemask()) < threshold) break;
+        }
+    }
+
+    if (STATS) {
+        // warp-reduce, one atomic per counter per warp
+        for (int o = 16; o > 0; o >>= 1) {
+            stNodeIters += __shfl_xor_sync(kFull, stNodeIters, o);
+            stNodeLanes += __shfl_xor_sync(kFull, stNodeLanes, o);
+            stTriIters += __shfl_xor_sync(kFull, stTriIters, o);
+            stTriLanes += __shfl_xor_sync(kFull, stTriLanes, o);
+            stFetches += __shfl_xor_sync(kFull, stFetches, o);
+        }
+        if (lane == 0) {
+            atomicAdd(p.stats + 0, stNodeIters); atomicAdd(p.stats + 1, stNodeLanes);
+            atomicAdd(p.stats + 2, stTriIters);  atomicAdd(p.stats + 3, stTriLanes);
+            atomicAdd(p.stats + 4, stFetches);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// launcher
+// ---------------------------------------------------------------------------------------------
+struct Variant { int block; int stackSmem; int minBlocks; };
+
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS>
+static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
+{
+    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS>;
+    int topNodes = ctx->cfg.top_nodes < 0 ? 512 : ctx->cfg.top_nodes;
+    if (topNodes > ctx->topNodesAvail) topNodes = ctx->topNodesAvail;
+    size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int);
+    // keep MIN_BLOCKS CTAs resident inside the 227 KB a CTA can opt into
+    const size_t smemBudget = (size_t)(227 * 1024) / MIN_BLOCKS - 1024;
+    while (topNodes > 0 && (size_t)topNodes * 64 + stackBytes > smemBudget) topNodes /= 2;
+    p.topF4 = topNodes * 4;
+    size_t smem = (size_t)p.topF4 * sizeof(float4) + stackBytes;
+    B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int blocksPerSm = 0;
+    B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, smem));
+    if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "trace kernel does not fit on an SM");
+    if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
+    long long grid = (long long)ctx->smCount * blocksPerSm;
+    const long long needed = ((long long)p.numRays + BLOCK - 1) / BLOCK;
+    if (grid > needed) grid = needed;
+    if (grid < 1) grid = 1;
+    B2RT_CUDA(ctx, cudaMemsetAsync(p.warpCounter, 0, sizeof(int), stream));
+    kern<<<(unsigned)grid, BLOCK, smem, stream>>>(p);
+    B2RT_CHECK_LAUNCH(ctx, "traceKernel");
+    return B2RT_OK;
+}
+
+template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS>
+static int launchFlags(b2rt_ctx* ctx, TraceParams& p, unsigned flags, cudaStream_t stream)
+{
+    const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
+    const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
+    if (flags & B2RT_TRACE_STATS) {
+        // the instrumented build always writes barycentrics (one kernel fewer to carry)
+        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream)
+                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+    }
+    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream)
+                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream)
+                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+}
+
+int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
+                cudaStream_t stream)
+{
+    TraceParams p;
+    p.rays = static_cast<const float4*>(rays);
+    p.results = static_cast<int4*>(results);
+    p.nodes = ctx->nodes;
+    p.woop = ctx->woop;
+    p.triIndex = ctx->triIndex;
+    p.numRays = (int)numRays;
+    p.topF4 = 0;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
+    p.warpCounter = ctx->warpCounter;
+    p.stats = ctx->statsDev;
+    if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 8 * sizeof(unsigned long long), stream));
+    switch (ctx->cfg.variant) {
+    default:
+    case 0: return launchFlags<12, 256, 5>(ctx, p, flags, stream);   // <= 48 regs, 40 warps/SM
+    case 1: return launchFlags<12, 256, 4>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM
+    case 2: return launchFlags<0, 256, 5>(ctx, p, flags, stream);    // stack entirely in local memory
+    case 3: return launchFlags<16, 128, 8>(ctx, p, flags, stream);   // small CTAs
+    case 4: return launchFlags<8, 512, 3>(ctx, p, flags, stream);    // big CTAs, 48 warps/SM (<= 40 regs)
+    case 5: return launchFlags<12, 256, 6>(ctx, p, flags, stream);   // <= 40 regs, 48 warps/SM
+    }
+}
+
+}  // namespace b2rt

@@ -1,0 +1,590 @@
+"""Host-side mirror of the reference's C++ interface for the ray-casting path.
+
+Same class and method names, argument meaning and error behaviour as the reference (paths
+under its src/):  Scene (rt/Scene.hh), BVH (rt/bvh/BVH.hh), CudaBVH (rt/cuda/CudaBVH.hh:86-137),
+RayBuffer (rt/ray/RayBuffer.hh:37-97), PixelTable (rt/ray/PixelTable.hh), RayGen
+(rt/ray/RayGen.hh:41-69), CudaTracer (rt/cuda/CudaTracer.hh:39-69) and the headless part of
+Renderer (rt/cuda/Renderer.hh:49-146).  Everything that computes runs in libb2rt.so through the
+C ABI (include/b2rt.h); PyTorch only owns device memory and streams.  There is no CPU path.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import (BuildParams, B2rtError, LAYOUT_COMPACT2, RAY_DTYPE, RESULT_DTYPE, TRACE_ANY_HIT,
+                   TRACE_STATS, TRACE_WRITE_BARY, TraceConfig, TraceStats, check, lib, np_ptr)
+
+SCENE_KINDS = {"blob": 0, "interior": 1, "knot": 2, "strands": 3}
+
+
+def fail(msg):
+    """FW::fail (framework/base/Defs.cc:41-54) prints and exits; here it raises."""
+    raise RuntimeError(msg)
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+# ---------------------------------------------------------------------------------------------
+class Context:
+    """One b2rt_ctx per device (replaces CudaModule::staticInit + the tracer's process globals)."""
+    _cache = {}
+
+    def __init__(self, device=0):
+        self.device = int(device)
+        h = C.c_void_p()
+        rc = lib().b2rt_create(self.device, C.byref(h))
+        if rc != 0:
+            raise B2rtError(rc, lib().b2rt_last_error(None).decode())
+        self.handle = h
+
+    @classmethod
+    def get(cls, device=None):
+        if device is None:
+            device = torch.cuda.current_device()
+        device = int(device)
+        if device not in cls._cache:
+            cls._cache[device] = Context(device)
+        return cls._cache[device]
+
+    def launch_count(self):
+        return int(lib().b2rt_launch_count(self.handle))
+
+    def sm_count(self):
+        sm = C.c_int()
+        check(lib().b2rt_device_info(self.handle, C.byref(sm), None, None), self.handle)
+        return sm.value
+
+    def set_trace_config(self, top_nodes=-1, fetch_threshold=-1, blocks_per_sm=-1, variant=0):
+        cfg = TraceConfig(top_nodes, fetch_threshold, blocks_per_sm, variant)
+        check(lib().b2rt_set_trace_config(self.handle, C.byref(cfg)), self.handle)
+
+    def torch_device(self):
+        return torch.device("cuda", self.device)
+
+
+# ---------------------------------------------------------------------------------------------
+class Scene:
+    """rt/Scene.hh: flat triangle list, vertex positions and per-triangle normals (Scene.cc:35-84)."""
+
+    def __init__(self, verts, tris, camera=None, name="mesh"):
+        self.verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 3)
+        self.tris = np.ascontiguousarray(tris, np.int32).reshape(-1, 3)
+        self.normals = np.empty((len(self.tris), 3), np.float32)
+        check(lib().b2rt_tri_normals(np_ptr(self.verts), np_ptr(self.tris), len(self.tris), np_ptr(self.normals)))
+        self.camera = camera        # dict(pos, forward, up, fov, near, far) or None
+        self.name = name
+        self._normals_dev = {}
+
+    @staticmethod
+    def generate(kind, target_tris, seed):
+        """Seeded procedural stand-in for a README scene (csrc/host/scenegen.cpp)."""
+        h = C.c_void_p()
+        check(lib().b2rt_scene_generate(SCENE_KINDS[kind], int(target_tris), C.c_uint64(seed), C.byref(h)))
+        try:
+            v, t = C.c_void_p(), C.c_void_p()
+            nv, nt = C.c_int(), C.c_int()
+            check(lib().b2rt_scene_arrays(h, C.byref(v), C.byref(nv), C.byref(t), C.byref(nt)))
+            verts = np.ctypeslib.as_array(C.cast(v, C.POINTER(C.c_float)), (nv.value, 3)).copy()
+            tris = np.ctypeslib.as_array(C.cast(t, C.POINTER(C.c_int32)), (nt.value, 3)).copy()
+            cam = np.empty(12, np.float32)
+            check(lib().b2rt_scene_camera(h, np_ptr(cam)))
+        finally:
+            lib().b2rt_scene_free(h)
+        camera = {"pos": cam[0:3].copy(), "forward": cam[3:6].copy(), "up": cam[6:9].copy(),
+                  "fov": float(cam[9]), "near": float(cam[10]), "far": float(cam[11])}
+        return Scene(verts, tris, camera, name="%s-%d" % (kind, target_tris))
+
+    def getNumTriangles(self):
+        return len(self.tris)
+
+    def getNumVertices(self):
+        return len(self.verts)
+
+    def getTriNormalBuffer_dev(self, device):
+        key = str(device)
+        if key not in self._normals_dev:
+            self._normals_dev[key] = torch.from_numpy(self.normals).to(device)
+        return self._normals_dev[key]
+
+    def init_camera_for_mesh(self):
+        """CameraControls::initForMesh (framework/3d/CameraControls.cc:330-350)."""
+        lo, hi = self.verts.min(0), self.verts.max(0)
+        size = float((hi - lo).max())
+        c = (lo + hi) * np.float32(0.5)
+        self.camera = {"pos": np.array([c[0], c[1], c[2] + np.float32(size) * np.float32(0.75)], np.float32),
+                       "forward": np.array([0, 0, -1], np.float32), "up": np.array([0, 1, 0], np.float32),
+                       "fov": 70.0, "near": float(np.float32(size) * np.float32(0.0005)),
+                       "far": float(np.float32(size) * np.float32(1.5))}
+        return self.camera
+
+    def write_obj(self, path):
+        with open(path, "w") as f:
+            for v in self.verts:
+                f.write("v %.9g %.9g %.9g\n" % (v[0], v[1], v[2]))
+            for t in self.tris:
+                f.write("f %d %d %d\n" % (t[0] + 1, t[1] + 1, t[2] + 1))
+
+
+def camera_matrices(camera, w, h):
+    """(origin, nscreenToWorld column-major) as Renderer::beginFrame computes (Renderer.cc:126-129)."""
+    origin = np.empty(3, np.float32)
+    m = np.empty(16, np.float32)
+    check(lib().b2rt_camera_matrices(np_ptr(np.ascontiguousarray(camera["pos"], np.float32)),
+                                     np_ptr(np.ascontiguousarray(camera["forward"], np.float32)),
+                                     np_ptr(np.ascontiguousarray(camera["up"], np.float32)),
+                                     C.c_float(camera["fov"]), C.c_float(camera["near"]), C.c_float(camera["far"]),
+                                     int(w), int(h), np_ptr(origin), np_ptr(m)))
+    return origin, m
+
+
+# ---------------------------------------------------------------------------------------------
+class BVH:
+    """rt/bvh/BVH.hh: SBVH over a Scene.  Built by csrc/host/bvh_builder.cpp; holds the Compact2
+    arrays (what CudaBVH(bvh, BVHLayout_Compact2) produces in the reference)."""
+
+    def __init__(self, scene=None, split_alpha=1.0e-5, min_leaf=1, max_leaf=8, threads=0, spatial_splits=True,
+                 _handle=None):
+        self.scene = scene
+        if _handle is None:
+            p = BuildParams(split_alpha, min_leaf, max_leaf, threads, 1 if spatial_splits else 0)
+            h = C.c_void_p()
+            check(lib().b2rt_bvh_build(np_ptr(scene.verts), len(scene.verts), np_ptr(scene.tris), len(scene.tris),
+                                       C.byref(p), C.byref(h)))
+            _handle = h
+        self._h = _handle
+        n, w, t = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        nb, wb, tb = C.c_size_t(), C.c_size_t(), C.c_size_t()
+        check(lib().b2rt_bvh_arrays(self._h, C.byref(n), C.byref(nb), C.byref(w), C.byref(wb), C.byref(t), C.byref(tb)))
+        self.nodes = np.ctypeslib.as_array(C.cast(n, C.POINTER(C.c_float)), (nb.value // 4,))
+        self.woop = np.ctypeslib.as_array(C.cast(w, C.POINTER(C.c_float)), (wb.value // 4,))
+        self.triIndex = np.ctypeslib.as_array(C.cast(t, C.POINTER(C.c_int32)), (tb.value // 4,))
+        a, b, c2, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        s = C.c_float()
+        check(lib().b2rt_bvh_stats(self._h, C.byref(a), C.byref(b), C.byref(c2), C.byref(s), C.byref(d)))
+        self.stats = {"numInnerNodes": a.value, "numLeafNodes": b.value, "numTris": c2.value, "SAHCost": s.value,
+                      "maxDepth": d.value}
+
+    def __del__(self):
+        try:
+            if self._h:
+                lib().b2rt_bvh_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def arrays(self):
+        return {"layout": LAYOUT_COMPACT2, "nodes": self.nodes, "woop": self.woop, "triIndex": self.triIndex}
+
+    def serialize(self, path):
+        """bvhcache file (Renderer.cc:176-211; CudaBVH.cc:113-116)."""
+        check(lib().b2rt_bvh_save(self._h, str(path).encode()))
+
+    @staticmethod
+    def load(path, scene=None):
+        h = C.c_void_p()
+        rc = lib().b2rt_bvh_load(str(path).encode(), C.byref(h))
+        if rc != 0:
+            raise B2rtError(rc, "cannot load BVH cache file %s" % path)
+        return BVH(scene, _handle=h)
+
+
+class CudaBVH:
+    """rt/cuda/CudaBVH.hh: the three device arrays of a Compact2 BVH (nodes, triWoop, triIndex)."""
+
+    def __init__(self, bvh, layout=LAYOUT_COMPACT2, device=None):
+        if isinstance(bvh, BVH):
+            arrays = bvh.arrays()
+        else:
+            arrays = bvh        # dict with nodes / woop / triIndex (e.g. read from a bvhcache file)
+        self.m_layout = int(arrays.get("layout", layout)) if layout == LAYOUT_COMPACT2 else int(layout)
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.m_nodes = torch.from_numpy(np.ascontiguousarray(arrays["nodes"], np.float32).copy()).to(self.device)
+        self.m_triWoop = torch.from_numpy(np.ascontiguousarray(arrays["woop"], np.float32).copy()).to(self.device)
+        self.m_triIndex = torch.from_numpy(np.ascontiguousarray(arrays["triIndex"], np.int32).copy()).to(self.device)
+
+    def getLayout(self):
+        return self.m_layout
+
+    def getNodeBuffer_dev(self):
+        return self.m_nodes
+
+    def getTriWoopBuffer_dev(self):
+        return self.m_triWoop
+
+    def getTriIndexBuffer_dev(self):
+        return self.m_triIndex
+
+
+# ---------------------------------------------------------------------------------------------
+class RayBuffer:
+    """rt/ray/RayBuffer.hh:37-97.  Device arrays: rays (32 B), results (16 B), idToSlot, slotToID."""
+
+    def __init__(self, n=0, closestHit=True, device=None):
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.m_size = 0
+        self.m_capacity = 0
+        self.m_needClosestHit = bool(closestHit)
+        self.m_rays = self.m_results = self.m_IDToSlot = self.m_slotToID = None
+        self.rayAABB = None
+        self.resize(n)
+
+    def getSize(self):
+        return self.m_size
+
+    def resize(self, n):
+        """RayBuffer.cc:53-81: shrinking is logical, growing reallocates (contents lost)."""
+        n = int(n)
+        assert n >= 0
+        if n <= self.m_capacity and self.m_rays is not None:
+            self.m_size = n
+            return
+        self.m_capacity = n
+        self.m_size = n
+        self.m_rays = torch.empty((max(n, 1), 8), dtype=torch.float32, device=self.device)
+        self.m_results = torch.empty((max(n, 1), 4), dtype=torch.int32, device=self.device)
+        self.m_IDToSlot = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
+        self.m_slotToID = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
+
+    def setNeedClosestHit(self, c):
+        self.m_needClosestHit = bool(c)
+
+    def getNeedClosestHit(self):
+        return self.m_needClosestHit
+
+    def getRayBuffer_dev(self):
+        return self.m_rays[:self.m_size]
+
+    def getResultBuffer_dev(self):
+        return self.m_results[:self.m_size]
+
+    def getIDToSlotBuffer_dev(self):
+        return self.m_IDToSlot[:self.m_size]
+
+    def getSlotToIDBuffer_dev(self):
+        return self.m_slotToID[:self.m_size]
+
+    def setRays(self, rays, ids=None):
+        """Upload a whole host array of rays (setRay slot by slot, RayBuffer.cc:227-235)."""
+        rays = np.ascontiguousarray(rays)
+        n = len(rays)
+        self.resize(n)
+        if n == 0:
+            return
+        self.m_rays[:n].copy_(torch.from_numpy(rays.view(np.float32).reshape(n, 8)))
+        if ids is None:
+            ar = torch.arange(n, dtype=torch.int32, device=self.device)
+            self.m_slotToID[:n].copy_(ar)
+            self.m_IDToSlot[:n].copy_(ar)
+        else:
+            ids = torch.from_numpy(np.ascontiguousarray(ids, np.int32)).to(self.device)
+            self.m_slotToID[:n].copy_(ids)
+            self.m_IDToSlot[ids.long()] = torch.arange(n, dtype=torch.int32, device=self.device)
+
+    def getRays(self):
+        return self.m_rays[:self.m_size].cpu().numpy().view(RAY_DTYPE).reshape(-1)
+
+    def getResults(self):
+        return self.m_results[:self.m_size].cpu().numpy().view(RESULT_DTYPE).reshape(-1)
+
+    def getResultsByID(self):
+        """results looked up through idToSlot (getResultForID, RayBuffer.hh:56-60)."""
+        res = self.getResults()
+        return res[self.m_IDToSlot[:self.m_size].cpu().numpy()]
+
+    def getRayAABB(self):
+        return self.rayAABB
+
+    def mortonSort(self, ctx=None):
+        """RayBuffer::mortonSort (RayBuffer.cc:256-324), on the device."""
+        ctx = ctx or Context.get(self.device.index)
+        if self.m_size == 0:
+            return
+        check(lib().b2rt_morton_sort(ctx.handle, _dptr(self.m_rays), _dptr(self.m_IDToSlot), _dptr(self.m_slotToID),
+                                     self.m_size, None, _stream_ptr()), ctx.handle)
+
+
+class PixelTable:
+    """rt/ray/PixelTable.hh: index <-> pixel LUTs (Morton-ordered 8x8 blocks)."""
+
+    def __init__(self):
+        self.m_size = (0, 0)
+        self.indexToPixel = None
+        self.pixelToIndex = None
+        self._dev = None
+
+    def setSize(self, size, device):
+        size = (int(size[0]), int(size[1]))
+        if size != self.m_size or self._dev is None:
+            self.m_size = size
+            n = size[0] * size[1]
+            self.indexToPixel = np.empty(n, np.int32)
+            self.pixelToIndex = np.empty(n, np.int32)
+            check(lib().b2rt_pixel_table(size[0], size[1], np_ptr(self.indexToPixel), np_ptr(self.pixelToIndex)))
+            self._dev = torch.from_numpy(self.indexToPixel).to(device)
+
+    def getIndexToPixel_dev(self):
+        return self._dev
+
+
+class RayGen:
+    """rt/ray/RayGen.hh:41-69."""
+
+    def __init__(self, maxBatchSize=8 * 1024 * 1024, ctx=None):
+        self.m_maxBatchSize = int(maxBatchSize)
+        self.m_pixelTable = PixelTable()
+        self.m_aoStartIdx = 0
+        self._ctx = ctx
+        self._libc_rand = _LibcRand()
+
+    def _context(self, device):
+        return self._ctx or Context.get(device.index)
+
+    def primary(self, orays, origin, nscreenToWorld, w, h, maxDist):
+        """RayGen::primary (RayGen.cc:50-73)."""
+        ctx = self._context(orays.device)
+        self.m_pixelTable.setSize((w, h), orays.device)
+        orays.resize(w * h)
+        orays.setNeedClosestHit(True)
+        origin = np.ascontiguousarray(origin, np.float32)
+        m = np.ascontiguousarray(nscreenToWorld, np.float32).reshape(16)
+        check(lib().b2rt_raygen_primary(ctx.handle, np_ptr(origin), np_ptr(m), int(w), int(h), C.c_float(maxDist),
+                                        _dptr(self.m_pixelTable.getIndexToPixel_dev()), _dptr(orays.m_rays),
+                                        _dptr(orays.m_IDToSlot), _dptr(orays.m_slotToID), _stream_ptr()), ctx.handle)
+
+    def batching(self, numInputRays, numSamples, newBatch):
+        """RayGen::batching (RayGen.cc:124-142).  Returns (continues, newBatch, lo, hi)."""
+        if newBatch:
+            newBatch = False
+            self.m_aoStartIdx = 0
+        if self.m_aoStartIdx == numInputRays:
+            return False, newBatch, 0, 0
+        lo = self.m_aoStartIdx
+        hi = min(numInputRays, lo + self.m_maxBatchSize // numSamples)
+        self.m_aoStartIdx = hi
+        return True, newBatch, lo, hi
+
+    def ao(self, orays, irays, scene, numSamples, maxDist, newBatch, randomSeed=0):
+        """RayGen::ao (RayGen.cc:77-120).  Returns (continues, newBatch).  As in the reference the
+        `randomSeed` argument is ignored and the seed is libc's rand() (RayGen.cc:106)."""
+        cont, newBatch, lo, hi = self.batching(irays.getSize(), numSamples, newBatch)
+        if not cont:
+            return False, newBatch
+        ctx = self._context(orays.device)
+        orays.resize((hi - lo) * numSamples)
+        orays.setNeedClosestHit(False)
+        seed = self._libc_rand.rand()
+        normals = scene.getTriNormalBuffer_dev(orays.device)       # uploaded once, not per batch (RayGen.cc:87-91)
+        check(lib().b2rt_raygen_ao(ctx.handle, lo, hi - lo, int(numSamples), C.c_float(maxDist), C.c_uint32(seed),
+                                   _dptr(irays.m_rays), _dptr(irays.m_results), _dptr(normals), _dptr(orays.m_rays),
+                                   _dptr(orays.m_IDToSlot), _dptr(orays.m_slotToID), _stream_ptr()), ctx.handle)
+        self.lastSeed = seed
+        return True, newBatch
+
+
+class _LibcRand:
+    """libc rand() with its default seed, which is what RayGen.cc:106 draws from (never srand()'ed)."""
+
+    def __init__(self):
+        self._libc = C.CDLL(None)
+        self._libc.srand(1)
+
+    def rand(self):
+        return int(self._libc.rand())
+
+
+# ---------------------------------------------------------------------------------------------
+class CudaTracer:
+    """rt/cuda/CudaTracer.hh:39-69."""
+
+    def __init__(self, ctx=None, device=None):
+        self._ctx = ctx or Context.get(device)
+        self.m_bvh = None
+        self.m_kernelConfig = None
+        self.writeBarycentrics = False
+        self.collectStats = False
+        self.initKernel()
+
+    def initKernel(self):
+        """CudaTracer.cc:84-115: Compact2, 32x4 blocks, persistent threads."""
+        self.m_kernelConfig = {"bvhLayout": LAYOUT_COMPACT2, "blockWidth": 32, "blockHeight": 4, "usePersistentThreads": 1}
+
+    def getDesiredBVHLayout(self):
+        return self.m_kernelConfig["bvhLayout"]
+
+    def setBVH(self, bvh):
+        """CudaTracer.hh:49 + the texture bind of CudaTracer.cc:142-146."""
+        self.m_bvh = bvh
+        if bvh is None:
+            return
+        if bvh.getLayout() != self.getDesiredBVHLayout():
+            return      # reported at traceBatch, like the reference
+        n, w, t = bvh.getNodeBuffer_dev(), bvh.getTriWoopBuffer_dev(), bvh.getTriIndexBuffer_dev()
+        check(lib().b2rt_set_bvh(self._ctx.handle, _dptr(n), n.numel() * 4, _dptr(w), w.numel() * 4, _dptr(t),
+                                 t.numel() * 4, bvh.getLayout(), 1), self._ctx.handle)
+
+    def traceBatch(self, rays):
+        """CudaTracer::traceBatch (CudaTracer.cc:119-178): returns the kernel time in MILLISECONDS
+        (cudaEventElapsedTime, kepler_dynamic_fetch.cu:471-473)."""
+        numRays = rays.getSize()
+        if not numRays:
+            return 0.0
+        if self.m_bvh is None:
+            fail("CudaTracer: No BVH!")
+        if self.m_bvh.getLayout() != self.getDesiredBVHLayout():
+            fail("CudaTracer: Incorrect BVH layout!")
+        flags = 0 if rays.getNeedClosestHit() else TRACE_ANY_HIT
+        if self.writeBarycentrics:
+            flags |= TRACE_WRITE_BARY
+        if self.collectStats:
+            flags |= TRACE_STATS
+        ms = C.c_float()
+        check(lib().b2rt_trace(self._ctx.handle, _dptr(rays.m_rays), _dptr(rays.m_results), numRays, flags,
+                               _stream_ptr(), C.byref(ms)), self._ctx.handle)
+        return ms.value
+
+    def traceBatchAsync(self, rays):
+        flags = 0 if rays.getNeedClosestHit() else TRACE_ANY_HIT
+        if self.writeBarycentrics:
+            flags |= TRACE_WRITE_BARY
+        if rays.getSize():
+            check(lib().b2rt_trace(self._ctx.handle, _dptr(rays.m_rays), _dptr(rays.m_results), rays.getSize(), flags,
+                                   _stream_ptr(), None), self._ctx.handle)
+
+    def traceHost(self, rays_host, results_host, anyHit=False):
+        """End-to-end call for HOST buffers (torch CPU tensors, ideally pinned): H2D, trace, D2H.
+        Returns (kernel_ms, total_ms)."""
+        n = rays_host.shape[0]
+        flags = (TRACE_ANY_HIT if anyHit else 0) | (TRACE_WRITE_BARY if self.writeBarycentrics else 0)
+        k, t = C.c_float(), C.c_float()
+        check(lib().b2rt_trace_host(self._ctx.handle, C.c_void_p(rays_host.data_ptr()), C.c_void_p(results_host.data_ptr()),
+                                    n, flags, C.byref(k), C.byref(t)), self._ctx.handle)
+        return k.value, t.value
+
+    def getStats(self):
+        s = TraceStats()
+        check(lib().b2rt_get_trace_stats(self._ctx.handle, C.byref(s)), self._ctx.handle)
+        return {n: getattr(s, n) for n, _ in s._fields_}
+
+
+def countHits(results_dev, ctx=None):
+    """launch_countHitsKernel (cuda/RendererKernels.cu:112-162,189-212)."""
+    ctx = ctx or Context.get(results_dev.device.index)
+    hits = C.c_int64()
+    check(lib().b2rt_count_hits(ctx.handle, _dptr(results_dev), results_dev.shape[0], C.byref(hits), _stream_ptr()), ctx.handle)
+    return hits.value
+
+
+# ---------------------------------------------------------------------------------------------
+class Renderer:
+    """Headless part of rt/cuda/Renderer.hh: the batch state machine around the tracer.
+    RayType as Renderer.hh:52-58."""
+    RayType_Primary, RayType_AO, RayType_Diffuse = 0, 1, 2
+
+    class Params:
+        def __init__(self):                 # Renderer.hh:68-74
+            self.rayType = Renderer.RayType_Primary
+            self.aoRadius = 1.0
+            self.numSamples = 32
+            self.sortSecondary = False
+
+    def __init__(self, frameSize, device=None):
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self._ctx = Context.get(self.device.index)
+        self.m_raygen = RayGen(1 << 21, self._ctx)          # Renderer.cc:46
+        self.m_tracer = CudaTracer(self._ctx)
+        self.m_params = Renderer.Params()
+        self.m_scene = None
+        self.m_bvh = None
+        self.m_hostBVH = None
+        self.m_ViewSize = (int(frameSize[0]), int(frameSize[1]))
+        self.m_primaryRays = RayBuffer(0, True, self.device)
+        self.m_secondaryRays = RayBuffer(0, True, self.device)
+        self.m_newBatch = True
+        self.m_batchRays = None
+        self.m_batchStart = 0
+        self.m_cameraFar = 0.0
+        self.m_buildParams = {"split_alpha": 1.0e-5}
+
+    def setMesh(self, scene):
+        if scene is self.m_scene:
+            return
+        self.m_scene = scene
+        self.m_bvh = None
+
+    def setParams(self, params):
+        self.m_params = params
+        self.m_tracer.initKernel()
+
+    def setBVH(self, host_bvh):
+        """Inject an already built BVH (stands in for the bvhcache hit of Renderer.cc:186-196)."""
+        self.m_hostBVH = host_bvh
+        self.m_bvh = CudaBVH(host_bvh, device=self.device)
+
+    def getCudaBVH(self):
+        """Renderer::getCudaBVH (Renderer.cc:157-217) without the file cache."""
+        if self.m_bvh is None:
+            self.m_hostBVH = BVH(self.m_scene, split_alpha=self.m_buildParams["split_alpha"], min_leaf=1, max_leaf=8)
+            self.m_bvh = CudaBVH(self.m_hostBVH, device=self.device)
+        return self.m_bvh
+
+    def beginFrame(self, camera):
+        """Renderer::beginFrame (Renderer.cc:112-152)."""
+        self.m_tracer.setBVH(self.getCudaBVH())
+        w, h = self.m_ViewSize
+        origin, m = camera_matrices(camera, w, h)
+        self.m_raygen.primary(self.m_primaryRays, origin, m, w, h, camera["far"])
+        if self.m_params.rayType != Renderer.RayType_Primary:
+            self.m_tracer.traceBatch(self.m_primaryRays)
+        self.m_cameraFar = camera["far"]
+        self.m_newBatch = True
+        self.m_batchRays = None
+        self.m_batchStart = 0
+
+    def getTotalNumRays(self):
+        """Renderer::getTotalNumRays (Renderer.cc:221-238): degenerate secondary rays are not counted."""
+        if self.m_params.rayType == Renderer.RayType_Primary:
+            return self.m_primaryRays.getSize()
+        return countHits(self.m_primaryRays.getResultBuffer_dev(), self._ctx) * self.m_params.numSamples
+
+    def nextBatch(self):
+        """Renderer::nextBatch (Renderer.cc:242-291)."""
+        if self.m_batchRays is not None:
+            self.m_batchStart += self.m_batchRays.getSize()
+        self.m_batchRays = None
+        p = self.m_params
+        if p.rayType == Renderer.RayType_Primary:
+            if not self.m_newBatch:
+                return False
+            self.m_newBatch = False
+            self.m_batchRays = self.m_primaryRays
+        elif p.rayType == Renderer.RayType_AO:
+            cont, self.m_newBatch = self.m_raygen.ao(self.m_secondaryRays, self.m_primaryRays, self.m_scene,
+                                                     p.numSamples, p.aoRadius, self.m_newBatch, 0)
+            if not cont:
+                return False
+            self.m_batchRays = self.m_secondaryRays
+        elif p.rayType == Renderer.RayType_Diffuse:
+            cont, self.m_newBatch = self.m_raygen.ao(self.m_secondaryRays, self.m_primaryRays, self.m_scene,
+                                                     p.numSamples, self.m_cameraFar, self.m_newBatch, 0)
+            if not cont:
+                return False
+            self.m_secondaryRays.setNeedClosestHit(True)
+            self.m_batchRays = self.m_secondaryRays
+        else:
+            return False
+        if p.sortSecondary and p.rayType != Renderer.RayType_Primary:
+            self.m_batchRays.mortonSort(self._ctx)
+        return True
+
+    def traceBatch(self):
+        """Renderer::traceBatch (Renderer.cc:295-300): kernel milliseconds of this batch."""
+        assert self.m_batchRays is not None
+        return self.m_tracer.traceBatch(self.m_batchRays)
