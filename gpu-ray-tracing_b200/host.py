@@ -588,3 +588,35 @@ class Renderer:
         """Renderer::traceBatch (Renderer.cc:295-300): kernel milliseconds of this batch."""
         assert self.m_batchRays is not None
         return self.m_tracer.traceBatch(self.m_batchRays)
+
+
+# ---------------------------------------------------------------------------------------------
+# the pieces of mortonSort and the reconstruction kernel, exposed for parity tests and the
+# headless image path
+def findAABB(rays_dev, ctx=None):
+    """launch_findAABBKernel (ray/RayBufferKernels.cu:74-140): (lo[3], hi[3]) of origins and end points."""
+    ctx = ctx or Context.get(rays_dev.device.index)
+    box = np.empty(6, np.float32)
+    check(lib().b2rt_find_aabb(ctx.handle, _dptr(rays_dev), rays_dev.shape[0], np_ptr(box), _stream_ptr()), ctx.handle)
+    return box[:3].copy(), box[3:].copy()
+
+
+def mortonKeys(rays_dev, lo, hi, ctx=None):
+    """launch_genMortonKeysKernel (ray/RayBufferKernels.cu:144-179): 28-byte MortonKey records."""
+    ctx = ctx or Context.get(rays_dev.device.index)
+    n = rays_dev.shape[0]
+    keys = torch.empty((max(n, 1), 7), dtype=torch.int32, device=rays_dev.device)
+    box = np.concatenate([np.asarray(lo, np.float32), np.asarray(hi, np.float32)])
+    check(lib().b2rt_morton_keys(ctx.handle, _dptr(rays_dev), n, np_ptr(box), _dptr(keys), _stream_ptr()), ctx.handle)
+    return keys[:n].cpu().numpy().view(_lib.KEY_DTYPE).reshape(-1)
+
+
+def reconstruct(mode, numRaysPerPrimary, firstPrimary, numPrimary, primaryRays, batchRays, triMaterialColor_dev,
+                triShadedColor_dev, pixels_dev, ctx=None):
+    """launch_reconstructKernel (cuda/RendererKernels.cu:60-108).  mode: 'primary' | 'ao' | 'diffuse'."""
+    ctx = ctx or Context.get(pixels_dev.device.index)
+    m = {"primary": 0, "ao": 1, "diffuse": 2}[mode]
+    check(lib().b2rt_reconstruct(ctx.handle, int(numRaysPerPrimary), int(firstPrimary), int(numPrimary), m,
+                                 _dptr(primaryRays.m_slotToID), _dptr(primaryRays.m_results), _dptr(batchRays.m_IDToSlot),
+                                 _dptr(batchRays.m_results), _dptr(triMaterialColor_dev), _dptr(triShadedColor_dev),
+                                 _dptr(pixels_dev), _stream_ptr()), ctx.handle)
