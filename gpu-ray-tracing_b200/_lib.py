@@ -28,6 +28,10 @@ class TraceStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("node_iters", "node_lanes", "tri_iters", "tri_lanes", "fetches", "rays")]
 
 
+class WorkCounters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("rays", "nodes", "tris", "leaves", "ustage", "vstage", "hits", "max_stack")]
+
+
 class TraceConfig(C.Structure):
     _fields_ = [("top_nodes", C.c_int), ("fetch_threshold", C.c_int), ("blocks_per_sm", C.c_int), ("variant", C.c_int)]
 
@@ -58,6 +62,7 @@ _SIGNATURES = {
     "b2rt_trace": (i32, [vp, vp, vp, i64, C.c_uint, vp, C.POINTER(f32)]),
     "b2rt_trace_host": (i32, [vp, vp, vp, i64, C.c_uint, C.POINTER(f32), C.POINTER(f32)]),
     "b2rt_get_trace_stats": (i32, [vp, C.POINTER(TraceStats)]),
+    "b2rt_count_work": (i32, [vp, vp, i64, i32, C.POINTER(WorkCounters), vp]),
     "b2rt_raygen_primary": (i32, [vp, vp, vp, i32, i32, f32, vp, vp, vp, vp, vp]),
     "b2rt_raygen_ao": (i32, [vp, i32, i32, i32, f32, u32, vp, vp, vp, vp, vp, vp, vp]),
     "b2rt_morton_sort": (i32, [vp, vp, vp, vp, i64, vp, vp]),

@@ -272,6 +272,17 @@ int b2rt_trace_host(b2rt_ctx* ctx, const void* raysHost, void* resultsHost, int6
     return B2RT_OK;
 }
 
+int b2rt_count_work(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, void* stream)
+{
+    if (!ctx || !out) return B2RT_ERR_ARG;
+    memset(out, 0, sizeof(*out));
+    if (numRays == 0) return B2RT_OK;
+    if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
+    if (numRays < 0 || numRays > 0x7fffffff || !rays) return setError(ctx, B2RT_ERR_ARG, "b2rt_count_work: bad ray buffer");
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    return countWork(ctx, rays, numRays, anyHit, out, static_cast<cudaStream_t>(stream));
+}
+
 int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out)
 {
     if (!ctx || !out) return B2RT_ERR_ARG;

@@ -80,6 +80,8 @@ extern std::string g_createError;
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
                 cudaStream_t stream);
 
+int countWork(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, cudaStream_t stream);
+
 // device helpers
 #ifdef __CUDACC__
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }

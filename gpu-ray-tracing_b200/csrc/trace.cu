@@ -289,4 +289,109 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// canonical work counters (b2rt_count_work): the scalar algorithm of oracle/b2rt_oracle.c's
+// b2o_trace_woop, one thread per ray, IEEE division -- counts, does not store hits
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict__ rays, int numRays, int anyHit,
+                                                       const float4* __restrict__ nodes, const float4* __restrict__ woop,
+                                                       unsigned long long* out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long cN = 0, cT = 0, cL = 0, cU = 0, cV = 0, cH = 0, cS = 0;
+    if (i < numRays) {
+        const float4 o = __ldg(rays + 2 * (size_t)i), d = __ldg(rays + 2 * (size_t)i + 1);
+        const float tmin = o.w;
+        float hitT = d.w;
+        const float ooeps = 8.271806125530277e-25f;
+        const float idirx = __fdiv_rn(1.0f, fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+        const float idiry = __fdiv_rn(1.0f, fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+        const float idirz = __fdiv_rn(1.0f, fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+        const float oodx = __fmul_rn(o.x, idirx), oody = __fmul_rn(o.y, idiry), oodz = __fmul_rn(o.z, idirz);
+        int stack[72];
+        int sp = 0, nodeAddr = 0, hitIndex = -1;
+        stack[0] = kSentinel;
+        while (nodeAddr != kSentinel) {
+            if (nodeAddr >= 0) {
+                const float4 n0xy = ldg4(nodes + nodeAddr), n1xy = ldg4(nodes + nodeAddr + 1), nz = ldg4(nodes + nodeAddr + 2), cn = ldg4(nodes + nodeAddr + 3);
+                cN++;
+                const float c0lox = __fmaf_rn(n0xy.x, idirx, -oodx), c0hix = __fmaf_rn(n0xy.y, idirx, -oodx);
+                const float c0loy = __fmaf_rn(n0xy.z, idiry, -oody), c0hiy = __fmaf_rn(n0xy.w, idiry, -oody);
+                const float c0loz = __fmaf_rn(nz.x, idirz, -oodz), c0hiz = __fmaf_rn(nz.y, idirz, -oodz);
+                const float c1loz = __fmaf_rn(nz.z, idirz, -oodz), c1hiz = __fmaf_rn(nz.w, idirz, -oodz);
+                const float c1lox = __fmaf_rn(n1xy.x, idirx, -oodx), c1hix = __fmaf_rn(n1xy.y, idirx, -oodx);
+                const float c1loy = __fmaf_rn(n1xy.z, idiry, -oody), c1hiy = __fmaf_rn(n1xy.w, idiry, -oody);
+                const float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), tmin));
+                const float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), hitT));
+                const float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), tmin));
+                const float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), hitT));
+                const bool t0 = c0max >= c0min, t1 = c1max >= c1min;
+                const int c0 = __float_as_int(cn.x), c1 = __float_as_int(cn.y);
+                if (!t0 && !t1) nodeAddr = stack[sp--];
+                else {
+                    nodeAddr = t0 ? c0 : c1;
+                    if (t0 && t1) {
+                        int farChild = c1;
+                        if (c1min < c0min) { farChild = nodeAddr; nodeAddr = c1; }
+                        stack[++sp] = farChild;
+                        if ((unsigned long long)sp > cS) cS = sp;
+                    }
+                }
+            } else {
+                cL++;
+                bool done = false;
+                for (int triAddr = ~nodeAddr;; triAddr += 3) {
+                    const float4 v00 = ldg4(woop + triAddr);
+                    if (__float_as_int(v00.x) == (int)0x80000000) break;
+                    const float4 v11 = ldg4(woop + triAddr + 1), v22 = ldg4(woop + triAddr + 2);
+                    cT++;
+                    const float Oz = __fmaf_rn(-o.z, v00.z, __fmaf_rn(-o.y, v00.y, __fmaf_rn(-o.x, v00.x, v00.w)));
+                    const float invDz = __fdiv_rn(1.0f, __fmaf_rn(d.z, v00.z, __fmaf_rn(d.y, v00.y, __fmul_rn(d.x, v00.x))));
+                    const float t = __fmul_rn(Oz, invDz);
+                    if (t > tmin && t < hitT) {
+                        cU++;
+                        const float Ox = __fmaf_rn(o.z, v11.z, __fmaf_rn(o.y, v11.y, __fmaf_rn(o.x, v11.x, v11.w)));
+                        const float Dx = __fmaf_rn(d.z, v11.z, __fmaf_rn(d.y, v11.y, __fmul_rn(d.x, v11.x)));
+                        const float u = __fmaf_rn(t, Dx, Ox);
+                        if (u >= 0.0f) {
+                            cV++;
+                            const float Oy = __fmaf_rn(o.z, v22.z, __fmaf_rn(o.y, v22.y, __fmaf_rn(o.x, v22.x, v22.w)));
+                            const float Dy = __fmaf_rn(d.z, v22.z, __fmaf_rn(d.y, v22.y, __fmul_rn(d.x, v22.x)));
+                            const float v = __fmaf_rn(t, Dy, Oy);
+                            if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                                hitT = t; hitIndex = triAddr;
+                                if (anyHit) { done = true; break; }
+                            }
+                        }
+                    }
+                }
+                nodeAddr = done ? kSentinel : stack[sp--];
+            }
+        }
+        cH = (hitIndex != -1) ? 1 : 0;
+    }
+    unsigned long long v[7] = { cN, cT, cL, cU, cV, cH, 0 };
+    for (int k = 0; k < 6; k++) {
+        for (int s = 16; s > 0; s >>= 1) v[k] += __shfl_xor_sync(kFull, v[k], s);
+        if ((threadIdx.x & 31) == 0 && v[k]) atomicAdd(out + 1 + k, v[k]);
+    }
+    for (int s = 16; s > 0; s >>= 1) { const unsigned long long t = __shfl_xor_sync(kFull, cS, s); cS = t > cS ? t : cS; }
+    if ((threadIdx.x & 31) == 0) atomicMax(out + 7, cS);
+}
+
+int countWork(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, cudaStream_t stream)
+{
+    B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 8 * sizeof(unsigned long long), stream));
+    countWorkKernel<<<(unsigned)((numRays + 255) / 256), 256, 0, stream>>>(static_cast<const float4*>(rays), (int)numRays, anyHit,
+                                                                          ctx->nodes, ctx->woop, ctx->statsDev);
+    B2RT_CHECK_LAUNCH(ctx, "countWorkKernel");
+    unsigned long long h[8];
+    B2RT_CUDA(ctx, cudaMemcpyAsync(h, ctx->statsDev, sizeof(h), cudaMemcpyDeviceToHost, stream));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(stream));
+    out->rays = (uint64_t)numRays; out->nodes = h[1]; out->tris = h[2]; out->leaves = h[3];
+    out->ustage = h[4]; out->vstage = h[5]; out->hits = h[6]; out->max_stack = h[7];
+    return B2RT_OK;
+}
+
 }  // namespace b2rt

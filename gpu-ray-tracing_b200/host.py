@@ -468,6 +468,13 @@ class CudaTracer:
                                     n, flags, C.byref(k), C.byref(t)), self._ctx.handle)
         return k.value, t.value
 
+    def countWork(self, rays):
+        """Canonical per-batch work counters (b2rt_count_work): N_n, N_t, N_l, N_u, N_v, hits."""
+        w = _lib.WorkCounters()
+        check(lib().b2rt_count_work(self._ctx.handle, _dptr(rays.m_rays), rays.getSize(),
+                                    0 if rays.getNeedClosestHit() else 1, C.byref(w), _stream_ptr()), self._ctx.handle)
+        return {n: getattr(w, n) for n, _ in w._fields_}
+
     def getStats(self):
         s = TraceStats()
         check(lib().b2rt_get_trace_stats(self._ctx.handle, C.byref(s)), self._ctx.handle)
@@ -620,3 +627,75 @@ def reconstruct(mode, numRaysPerPrimary, firstPrimary, numPrimary, primaryRays, 
                                  _dptr(primaryRays.m_slotToID), _dptr(primaryRays.m_results), _dptr(batchRays.m_IDToSlot),
                                  _dptr(batchRays.m_results), _dptr(triMaterialColor_dev), _dptr(triShadedColor_dev),
                                  _dptr(pixels_dev), _stream_ptr()), ctx.handle)
+
+
+# ---------------------------------------------------------------------------------------------
+# camera signatures: the --camera="..." strings of grtcmdline.txt / test.txt
+# (CameraControls::encodeSignature / decodeSignature, framework/3d/CameraControls.cc:354-419,
+#  bit packing :472-555: 6 bits per character, floats as 6 characters little-end first)
+def _enc_bits(v):
+    base = ord('/') if v < 12 else (ord('A') - 12 if v < 38 else ord('a') - 38)
+    return chr(v + base)
+
+
+def _enc_float(f):
+    bits = int(np.float32(f).view(np.uint32))
+    return "".join(_enc_bits((bits >> i) & 0x3F) for i in range(0, 32, 6))
+
+
+def _enc_dir(v):
+    v = np.asarray(v, np.float32)
+    a = np.abs(v)
+    axis = 0 if a[0] >= max(a[1], a[2]) else (1 if a[1] >= a[2] else 2)
+    tuv = v if axis == 0 else (np.array([v[1], v[2], v[0]], np.float32) if axis == 1 else np.array([v[2], v[0], v[1]], np.float32))
+    face = axis | (0 if tuv[0] >= 0 else 4)
+    if tuv[1] == 0 and tuv[2] == 0:
+        return _enc_bits(face | 8)
+    return _enc_bits(face) + _enc_float(tuv[1] / abs(tuv[0])) + _enc_float(tuv[2] / abs(tuv[0]))
+
+
+def encode_camera_signature(camera, speed=1.0, keep_aligned=False):
+    p = camera["pos"]
+    return ('"' + _enc_float(p[0]) + _enc_float(p[1]) + _enc_float(p[2]) + _enc_dir(camera["forward"]) + _enc_dir(camera["up"]) +
+            _enc_float(speed) + _enc_float(camera["fov"]) + _enc_float(camera["near"]) + _enc_float(camera["far"]) +
+            _enc_bits(1 if keep_aligned else 0) + '",')
+
+
+def decode_camera_signature(sig):
+    s = sig.strip()
+    if s.startswith('"'):
+        s = s[1:]
+    pos = [0]
+
+    def bits():
+        c = s[pos[0]]
+        pos[0] += 1
+        if '/' <= c <= ':':
+            return ord(c) - ord('/')
+        if 'A' <= c <= 'Z':
+            return ord(c) - ord('A') + 12
+        if 'a' <= c <= 'z':
+            return ord(c) - ord('a') + 38
+        fail("CameraControls: Invalid signature!")
+
+    def flt():
+        b = 0
+        for i in range(0, 32, 6):
+            b |= bits() << i
+        return np.uint32(b & 0xFFFFFFFF).view(np.float32)
+
+    def direction():
+        face = bits()
+        t = np.array([1.0 if (face & 4) == 0 else -1.0, flt() if (face & 8) == 0 else 0.0, 0.0], np.float32)
+        t[2] = flt() if (face & 8) == 0 else 0.0
+        l = np.float32(0)
+        for k in range(3):
+            l = np.float32(l + t[k] * t[k])
+        t = t * (np.float32(1) / np.sqrt(l))
+        return t if (face & 3) == 0 else (np.array([t[2], t[0], t[1]], np.float32) if (face & 3) == 1 else np.array([t[1], t[2], t[0]], np.float32))
+
+    px, py, pz = flt(), flt(), flt()
+    fwd, up = direction(), direction()
+    flt()       # speed
+    fov, near, far = flt(), flt(), flt()
+    return {"pos": np.array([px, py, pz], np.float32), "forward": fwd, "up": up, "fov": float(fov), "near": float(near), "far": float(far)}

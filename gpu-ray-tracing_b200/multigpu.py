@@ -1,0 +1,90 @@
+"""Multi-GPU plumbing: one process per GPU, BVH replicated, ray batches sharded.
+
+The reference is single-GPU (no NCCL, no peer access -- SURVEY.md 2a).  Rays are independent, so
+the path shards with no exchange step inside a trace:
+  * scene: rank 0 builds the BVH on its host and the three Compact2 arrays travel to every other
+    rank with torch.distributed.broadcast (NCCL over NVLink on the GPU box, gloo in CPU tests);
+  * rays: each rank takes the contiguous slice [lo, hi) of a batch -- after the Morton sort, so a
+    slice stays spatially coherent -- or generates its own slice on the device;
+  * hits: all_gather of the 16-byte result records (padded to equal slice sizes), and an
+    all_reduce of the hit / ray counters and of the per-rank kernel milliseconds (max).
+No collective runs inside the timed trace.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(n, rank, world_size):
+    """Contiguous slice of n units for `rank`: sizes differ by at most one, union is [0, n)."""
+    base, rem = divmod(int(n), int(world_size))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def _comm_device(device):
+    """Tensors must live where the backend can see them: GPU for nccl, CPU for gloo."""
+    if dist.get_backend() == "nccl":
+        return torch.device(device)
+    return torch.device("cpu")
+
+
+def broadcast_bvh(arrays, device, src=0):
+    """Replicate the Compact2 arrays of rank `src` on every rank.  `arrays` is a dict with numpy
+    nodes / woop / triIndex on `src` and may be None elsewhere.  Returns the dict on every rank."""
+    rank, ws = world()
+    if ws == 1:
+        return arrays
+    cd = _comm_device(device)
+    sizes = torch.zeros(3, dtype=torch.int64, device=cd)
+    if rank == src:
+        sizes = torch.tensor([arrays["nodes"].size, arrays["woop"].size, arrays["triIndex"].size],
+                             dtype=torch.int64, device=cd)
+    dist.broadcast(sizes, src)
+    n_nodes, n_woop, n_tri = (int(v) for v in sizes.tolist())
+    out = {"layout": 5}
+    for key, n, dt, npdt in (("nodes", n_nodes, torch.float32, np.float32), ("woop", n_woop, torch.float32, np.float32),
+                             ("triIndex", n_tri, torch.int32, np.int32)):
+        if rank == src:
+            t = torch.from_numpy(np.ascontiguousarray(arrays[key], npdt)).to(cd)
+        else:
+            t = torch.empty(n, dtype=dt, device=cd)
+        dist.broadcast(t, src)
+        out[key] = t.cpu().numpy()
+    return out
+
+
+def gather_results(local_results, total, device):
+    """all_gather the per-rank slices of 16-byte result records (int32 [n_r, 4]) into [total, 4],
+    in rank order.  Slices are padded to the largest slice for the collective."""
+    rank, ws = world()
+    if ws == 1:
+        return local_results
+    cd = _comm_device(device)
+    per = max(shard_range(total, r, ws)[1] - shard_range(total, r, ws)[0] for r in range(ws))
+    pad = torch.zeros((per, 4), dtype=torch.int32, device=cd)
+    pad[: local_results.shape[0]] = local_results.to(cd)
+    out = torch.empty((ws * per, 4), dtype=torch.int32, device=cd)
+    dist.all_gather_into_tensor(out, pad) if dist.get_backend() == "nccl" else \
+        dist.all_gather(list(out.view(ws, per, 4).unbind(0)), pad)
+    parts = []
+    for r in range(ws):
+        lo, hi = shard_range(total, r, ws)
+        parts.append(out[r * per: r * per + (hi - lo)])
+    return torch.cat(parts, 0)
+
+
+def reduce_stats(values, device, op="sum"):
+    """all_reduce a list of python numbers (sum or max) -- hit counts, ray counts, kernel ms."""
+    rank, ws = world()
+    if ws == 1:
+        return list(values)
+    t = torch.tensor(values, dtype=torch.float64, device=_comm_device(device))
+    dist.all_reduce(t, dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX)
+    return t.tolist()

@@ -1,0 +1,149 @@
+"""The benchmark configurations of BASELINE.json as seeded synthetic workloads.
+
+  c1  144 500-tri blob,      1024x768 primary rays                      (the CPU-runnable case)
+  c2  350 949-tri interior,  1024x768 primary + 1-bounce diffuse        (the 1-GPU headline)
+  c3  910 348-tri knot,      AO 32 rays/pixel, any-hit, Morton-sorted 2^21-ray batches
+  c4  6 469 561-tri strands, primary + incoherent diffuse (divergence stress)
+  c5  910 348-tri knot,      one 64 Mi-ray diffuse batch, BVH replicated, rays sharded over ranks
+Seeds are 20260101 + config number.  Everything here calls the product's public interface
+(host.py -> libb2rt.so); nothing touches oracle/.
+"""
+import os
+import time
+
+import numpy as np
+import torch
+
+from .host import BVH, CudaBVH, CudaTracer, Context, RayBuffer, RayGen, Scene, camera_matrices, countHits
+
+CONFIGS = {
+    "c1": dict(kind="blob", tris=144500, seed=20260102, size=(1024, 768), ray_type="primary", samples=1, sort=False),
+    "c2": dict(kind="interior", tris=350949, seed=20260103, size=(1024, 768), ray_type="diffuse", samples=1, sort=False),
+    "c3": dict(kind="knot", tris=910348, seed=20260104, size=(1024, 768), ray_type="ao", samples=32, sort=True),
+    "c4": dict(kind="strands", tris=6469561, seed=20260105, size=(1024, 768), ray_type="diffuse", samples=1, sort=False),
+    "c5": dict(kind="knot", tris=910348, seed=20260104, size=(1024, 768), ray_type="diffuse", samples=86, sort=False,
+               total_rays=64 * 1024 * 1024),
+    # small stand-in used by smoke() and the tests
+    "tiny": dict(kind="interior", tris=20000, seed=7, size=(160, 120), ray_type="diffuse", samples=2, sort=False),
+}
+
+CACHE_DIR = os.environ.get("B2RT_BVH_CACHE", "/tmp/b2rt_bvhcache")
+
+
+def describe(name):
+    c = CONFIGS[name]
+    return "%s: procedural %s %d tris, %dx%d %s%s%s" % (
+        name, c["kind"], c["tris"], c["size"][0], c["size"][1], c["ray_type"],
+        " x%d" % c["samples"] if c["ray_type"] != "primary" else "", ", Morton-sorted" if c["sort"] else "")
+
+
+def build_scene_and_bvh(name, use_cache=True, log=None):
+    """Scene + host BVH for a config; the BVH goes through a bvhcache file (Renderer.cc:176-211)."""
+    c = CONFIGS[name]
+    t0 = time.time()
+    scene = Scene.generate(c["kind"], c["tris"], c["seed"])
+    t1 = time.time()
+    path = os.path.join(CACHE_DIR, "%s-%d-%d.dat" % (c["kind"], c["tris"], c["seed"]))
+    bvh = None
+    if use_cache and os.path.exists(path):
+        try:
+            bvh = BVH.load(path, scene)
+        except Exception:
+            bvh = None
+    if bvh is None:
+        bvh = BVH(scene)
+        if use_cache:
+            try:
+                os.makedirs(CACHE_DIR, exist_ok=True)
+                bvh.serialize(path)
+            except Exception:
+                pass
+    if log:
+        log("scene %s: %d tris in %.2fs, BVH (%d inner nodes, %d Woop rows) in %.2fs" % (
+            scene.name, scene.getNumTriangles(), t1 - t0, bvh.nodes.size // 16, bvh.woop.size // 4, time.time() - t1))
+    return scene, bvh
+
+
+class Frame:
+    """One frame of a config on one device: primary rays traced, then the list of secondary
+    batches (as Renderer::beginFrame / nextBatch produce them, Renderer.cc:112-291), all resident
+    in HBM.  `batches` holds (RayBuffer, counted_rays) pairs ready to be traced and timed."""
+
+    def __init__(self, name, scene, bvh_arrays, device, ctx=None, shard=(0, 1), max_batch=1 << 21):
+        c = CONFIGS[name]
+        self.name, self.cfg, self.scene = name, c, scene
+        self.device = torch.device(device)
+        self.ctx = ctx or Context.get(self.device.index)
+        self.tracer = CudaTracer(self.ctx)
+        self.cuda_bvh = CudaBVH(bvh_arrays, device=self.device)
+        self.tracer.setBVH(self.cuda_bvh)
+        self.raygen = RayGen(max_batch, self.ctx)
+        w, h = c["size"]
+        origin, m = camera_matrices(scene.camera, w, h)
+        self.primary = RayBuffer(0, True, self.device)
+        self.raygen.primary(self.primary, origin, m, w, h, scene.camera["far"])
+        self.batches = []
+        rank, ws = shard
+        if c["ray_type"] == "primary":
+            self.batches.append((self.primary, w * h))
+            return
+        self.tracer.traceBatch(self.primary)
+        hits = countHits(self.primary.getResultBuffer_dev(), self.ctx)
+        samples = c["samples"]
+        far = scene.camera["far"]
+        if c["ray_type"] == "ao":
+            lo, hi = scene.verts.min(0), scene.verts.max(0)
+            max_dist = 0.05 * float(np.linalg.norm(hi - lo))        # aoRadius = 5 % of the scene diagonal
+        else:
+            max_dist = far
+        total = c.get("total_rays")
+        if total:
+            # C5: ONE buffer of `total` diffuse rays (primaries x samples, truncated), this rank's slice
+            from .multigpu import shard_range
+            n_prim_needed = (total + samples - 1) // samples
+            big = RayGen(1 << 30, self.ctx)
+            lo_r, hi_r = shard_range(total, rank, ws)
+            p_lo, p_hi = lo_r // samples, min((hi_r + samples - 1) // samples, n_prim_needed)
+            sub = _slice_buffer(self.primary, p_lo, p_hi)
+            sec = RayBuffer(0, True, self.device)
+            big.ao(sec, sub, scene, samples, max_dist, True)
+            sec.setNeedClosestHit(True)
+            off = lo_r - p_lo * samples
+            sec = _slice_buffer(sec, off, off + (hi_r - lo_r), closest=True)
+            counted = int((sec.getRayBuffer_dev()[:, 7] >= 0).sum().item())
+            self.batches.append((sec, counted))
+            return
+        newBatch = True
+        while True:
+            sec = RayBuffer(0, True, self.device)
+            cont, newBatch = self.raygen.ao(sec, self.primary, scene, samples, max_dist, newBatch)
+            if not cont:
+                break
+            sec.setNeedClosestHit(c["ray_type"] == "diffuse")
+            if c["sort"]:
+                sec.mortonSort(self.ctx)
+            counted = int((sec.getRayBuffer_dev()[:, 7] >= 0).sum().item())     # degenerate rays have tmax = -1
+            self.batches.append((sec, counted))
+        assert sum(b[1] for b in self.batches) == hits * samples               # Renderer.cc:221-238
+
+    def counted_rays(self):
+        return sum(b[1] for b in self.batches)
+
+    def launched_rays(self):
+        return sum(b[0].getSize() for b in self.batches)
+
+    def trace_all(self):
+        """Trace every batch once; returns the summed kernel milliseconds (App.cc:194-204)."""
+        return sum(self.tracer.traceBatch(rb) for rb, _ in self.batches)
+
+
+def _slice_buffer(rb, lo, hi, closest=None):
+    out = RayBuffer(0, rb.getNeedClosestHit() if closest is None else closest, rb.device)
+    n = hi - lo
+    out.resize(n)
+    out.m_rays[:n].copy_(rb.m_rays[lo:hi])
+    out.m_results[:n].copy_(rb.m_results[lo:hi])
+    ar = torch.arange(n, dtype=torch.int32, device=rb.device)
+    out.m_IDToSlot[:n].copy_(ar)
+    out.m_slotToID[:n].copy_(ar)
+    return out

@@ -114,6 +114,17 @@ int b2rt_trace_host(b2rt_ctx* ctx, const void* rays_host, void* results_host, in
 /* counters of the last B2RT_TRACE_STATS launch (synchronises) */
 int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out);
 
+/* Algorithmic work of a batch: per-ray counters of the CANONICAL traversal (near-first ordered
+ * stack traversal of the Compact2 arrays, Woop test, closest-hit pruning or any-hit exit, no
+ * speculation, no postponement, IEEE division) summed over the batch -- the N_n, N_t, N_l, N_u,
+ * N_v, h of SURVEY.md 8(d) from which bench.py computes the roofline's algorithmic bytes.  A plain
+ * one-thread-per-ray kernel, not the production tracer.  Synchronous. */
+typedef struct {
+    uint64_t rays, nodes, tris, leaves, ustage, vstage, hits, max_stack;
+} b2rt_work_counters;
+int b2rt_count_work(b2rt_ctx* ctx, const void* rays_dev, int64_t num_rays, int any_hit,
+                    b2rt_work_counters* out, void* stream);
+
 /* ---- ray generation --------------------------------------------------------------------- */
 /* replaces launch_rayGenPrimaryKernel (ray/RayGenKernels.hh:40-51,107-109; RayGenKernels.cu:79-113).
  * nscreen_to_world is column-major like FW::Mat4f.  Writes w*h rays and both id maps. */

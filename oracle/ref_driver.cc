@@ -144,8 +144,9 @@ static void usage(void)
         "        [--camera-sig S | --camera-auto] [--size W H] [--camera-out F]\n"
         "        [--primary-out PREFIX]            rays via RayGen::primary -> PREFIX.rays/.slot2id\n"
         "        [--rays-in F [--any-hit]]         trace these instead of the primaries\n"
-        "        [--results-out F] [--procs P] [--limit N]   BVH::trace, timed\n"
+        "        [--results-out F] [--procs P] [--limit N] [--repeat K]   BVH::trace, timed (one JSON line per repeat)\n"
         "        [--ao-out PREFIX --samples S --max-dist D [--sort]]   RayGen::ao batches from the primaries\n"
+        "        [--trace-secondary [--secondary-closest] [--secondary-results-out F]]  time BVH::trace on the first secondary batch\n"
         "        [--sort-in F --sort-out PREFIX]   RayBuffer::mortonSort\n");
     exit(2);
 }
@@ -153,9 +154,10 @@ static void usage(void)
 int main(int argc, char** argv)
 {
     std::string obj, sceneOut, bvhOut, camSig, camOut, primOut, raysIn, resOut, aoOut, sortIn, sortOut;
-    bool camAuto = false, anyHit = false, aoSort = false;
+    bool camAuto = false, anyHit = false, aoSort = false, secTrace = false, secClosest = false;
+    std::string secResOut;
     float alpha = 1.0e-5f, maxDist = 0.0f;
-    int W = 1024, H = 768, procs = 1, samples = 1, limit = -1;
+    int W = 1024, H = 768, procs = 1, samples = 1, limit = -1, repeat = 1;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() -> const char* { if (i + 1 >= argc) usage(); return argv[++i]; };
@@ -173,10 +175,14 @@ int main(int argc, char** argv)
         else if (a == "--results-out") resOut = next();
         else if (a == "--procs") procs = atoi(next());
         else if (a == "--limit") limit = atoi(next());
+        else if (a == "--repeat") repeat = atoi(next());
         else if (a == "--ao-out") aoOut = next();
         else if (a == "--samples") samples = atoi(next());
         else if (a == "--max-dist") maxDist = (float)atof(next());
         else if (a == "--sort") aoSort = true;
+        else if (a == "--trace-secondary") secTrace = true;       /* time BVH::trace on the first secondary batch */
+        else if (a == "--secondary-closest") secClosest = true;   /* Diffuse: setNeedClosestHit(true), Renderer.cc:277 */
+        else if (a == "--secondary-results-out") secResOut = next();
         else if (a == "--sort-in") sortIn = next();
         else if (a == "--sort-out") sortOut = next();
         else usage();
@@ -264,7 +270,7 @@ int main(int argc, char** argv)
         for (S32 i = 0; i < n; i++) primary.setRay(i, tmp[i]);
         memcpy(primary.getRayBuffer_dev(), tmp.data(), (size_t)n * sizeof(Ray));
         havePrimary = true;
-    } else if (!primOut.empty() || !resOut.empty() || !aoOut.empty()) {
+    } else if (!primOut.empty() || !resOut.empty() || !aoOut.empty() || secTrace) {
         raygen.primary(primary, camera.getPosition(), nscreenToWorld, W, H, camera.getFar());
         devToHost(primary);
         havePrimary = true;
@@ -274,17 +280,41 @@ int main(int argc, char** argv)
         }
     }
 
-    if (havePrimary && (!resOut.empty() || !aoOut.empty())) {
-        double sec = traceTimed(bvh, primary, procs);
+    if (havePrimary && (!resOut.empty() || !aoOut.empty() || secTrace)) {
         S32 n = primary.getSize();
+        double sec = 0.0;
+        for (int rep = 0; rep < repeat; rep++) {
+        sec = traceTimed(bvh, primary, procs);
         fprintf(stdout, "{\"rays\": %d, \"trace_s\": %.6f, \"mrays_per_s\": %.4f, \"procs\": %d, \"closest\": %d}\n",
                 n, sec, n / sec * 1e-6, procs, primary.getNeedClosestHit() ? 1 : 0);
+        fflush(stdout);
+        }
         if (!resOut.empty())
             dumpResults(resOut, (const RayResult*)primary.getResultBuffer().getPtr(), n);
     }
 
     /* Renderer::nextBatch -- Renderer.cc:242-291: AO / diffuse batches from the primary hits */
-    if (!aoOut.empty()) {
+    if (secTrace) {
+        resultsHostToDev(primary);
+        RayBuffer secondary;
+        bool newBatch = true;
+        if (raygen.ao(secondary, primary, scene, samples, maxDist, newBatch, 0)) {
+            if (secClosest) secondary.setNeedClosestHit(true);
+            if (aoSort) secondary.mortonSort();
+            if (limit >= 0 && limit < secondary.getSize()) secondary.resize(limit);
+            devToHost(secondary);
+            S32 n = secondary.getSize(), counted = 0;
+            for (S32 i = 0; i < n; i++) if (secondary.getRayForSlot(i).tmax >= 0.0f) counted++;
+            for (int rep = 0; rep < repeat; rep++) {
+                double sec = traceTimed(bvh, secondary, procs);
+                fprintf(stdout, "{\"stage\": \"secondary\", \"rays\": %d, \"counted\": %d, \"trace_s\": %.6f, \"mrays_per_s\": %.4f, \"procs\": %d, \"closest\": %d}\n",
+                        n, counted, sec, counted / sec * 1e-6, procs, secondary.getNeedClosestHit() ? 1 : 0);
+                fflush(stdout);
+            }
+            if (!secResOut.empty()) dumpResults(secResOut, (const RayResult*)secondary.getResultBuffer().getPtr(), n);
+            if (!aoOut.empty()) dumpRays(aoOut + ".rays", (const Ray*)secondary.getRayBuffer().getPtr(), n);
+        }
+    } else if (!aoOut.empty()) {
         resultsHostToDev(primary);
         RayBuffer secondary;
         bool newBatch = true;

@@ -282,3 +282,56 @@ def run_ref_cpu(*args):
     """Run oracle/_ref/ref_cpu (the reference's own host code); returns its stdout."""
     r = subprocess.run([REF_CPU] + [str(a) for a in args], check=True, capture_output=True, text=True)
     return r.stdout
+
+
+# ---------------------------------------------------------------------------------------------
+# the reference's own CUDA tracer, compatibility build (oracle/_ref/libref_gpu.so, needs a GPU)
+# ---------------------------------------------------------------------------------------------
+REF_GPU_SO = os.path.join(ORACLE_DIR, "_ref", "libref_gpu.so")
+
+
+def have_ref_gpu():
+    return os.path.exists(REF_GPU_SO)
+
+
+class RefGpuTracer:
+    """kepler_dynamic_fetch `trace` through its own launcher (kepler_dynamic_fetch.cu:417-474).
+    Arguments are torch CUDA tensors.  `warps`: 720 is the reference's literal launch
+    (CudaTracer.cc:156); pass SM count x resident warps for the scaled variant."""
+
+    def __init__(self):
+        self.lib = C.CDLL(REF_GPU_SO)
+        self.lib.launch_tracingKernel.restype = C.c_float
+        self.lib.launch_tracingKernel.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_bool] + [C.c_void_p] * 10
+        self.lib.bind_CudaBVHTexture.restype = None
+        self.lib.bind_CudaBVHTexture.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+        self._bvh = None
+
+    def set_bvh(self, nodes, woop, tri_index):
+        # the reference reads three rows before it tests the terminator (texture fetches return 0
+        # out of range); with plain loads the Woop array needs two rows of padding
+        import torch
+        woop = torch.cat([woop.reshape(-1), torch.zeros(8, dtype=woop.dtype, device=woop.device)])
+        self._bvh = (nodes, woop, tri_index)
+        self.lib.bind_CudaBVHTexture(nodes.data_ptr(), nodes.numel() * 4, woop.data_ptr(), woop.numel() * 4,
+                                     tri_index.data_ptr(), tri_index.numel() * 4)
+
+    def trace(self, rays, results, any_hit=False, warps=720):
+        """Returns the kernel milliseconds the reference's launcher measures (cudaEvents, :449-473)."""
+        nodes, woop, tri = self._bvh
+        block = (C.c_int * 2)(32, 4)                      # CudaTracer.cc:105-107 asks for 32x4
+        threads = int(warps) * 32
+        # the launcher prints its grid each call (:447); keep stdout clean for bench.py's JSON line
+        fd = os.dup(1)
+        devnull = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(devnull, 1)
+        try:
+            ms = self.lib.launch_tracingKernel(threads, block, rays.shape[0], bool(any_hit), rays.data_ptr(),
+                                               results.data_ptr(), nodes.data_ptr(), nodes.data_ptr(), nodes.data_ptr(),
+                                               nodes.data_ptr(), woop.data_ptr(), woop.data_ptr(), woop.data_ptr(),
+                                               tri.data_ptr())
+        finally:
+            os.dup2(fd, 1)
+            os.close(fd)
+            os.close(devnull)
+        return float(ms)

@@ -1,0 +1,90 @@
+"""Tuning / comparison harness (not the bench): times the traversal kernel's variants and the
+reference's CUDA tracer (oracle/_ref/libref_gpu.so) on a config's batches, checks parity between
+them.  Usage: python tools/explore.py c2 [variants...]"""
+import importlib
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+b2rt = importlib.import_module("gpu-ray-tracing_b200")
+wl = importlib.import_module("gpu-ray-tracing_b200.workloads")
+import oracle_lib as O
+
+
+def median_ms(fn, warm=3, reps=7):
+    for _ in range(warm):
+        fn()
+    return float(np.median([fn() for _ in range(reps)]))
+
+
+def main():
+    name = sys.argv[1] if len(sys.argv) > 1 else "c2"
+    configs = [a for a in sys.argv[2:]]
+    ctx = b2rt.Context.get(0)
+    scene, bvh = wl.build_scene_and_bvh(name, log=lambda s: print(s, flush=True))
+    frame = wl.Frame(name, scene, bvh.arrays(), "cuda:0", ctx)
+    counted = frame.counted_rays()
+    print("batches", [(b.getSize(), c) for b, c in frame.batches], flush=True)
+    rb = frame.batches[0][0]
+    work = frame.tracer.countWork(rb)
+    n = work["rays"]
+    print("work/ray: nodes %.1f tris %.1f leaves %.1f hits %.3f maxstack %d" % (
+        work["nodes"] / n, work["tris"] / n, work["leaves"] / n, work["hits"] / n, work["max_stack"]))
+    out = {}
+    # reference CUDA tracer
+    if O.have_ref_gpu():
+        ref = O.RefGpuTracer()
+        ref.set_bvh(frame.cuda_bvh.m_nodes, frame.cuda_bvh.m_triWoop, frame.cuda_bvh.m_triIndex)
+        sm = ctx.sm_count()
+        for label, warps in (("ref720", 720), ("ref_scaled40", sm * 40), ("ref_scaled32", sm * 32), ("ref_scaled48", sm * 48)):
+            res = [torch.zeros_like(b.m_results) for b, _ in frame.batches]
+            ms = median_ms(lambda: sum(ref.trace(b.getRayBuffer_dev(), r, not b.getNeedClosestHit(), warps)
+                                       for (b, _), r in zip(frame.batches, res)))
+            out[label] = counted / ms / 1e3
+            print("%-16s %8.3f ms  %9.1f Mrays/s" % (label, ms, out[label]), flush=True)
+        ref_res = res
+    sweeps = configs or ["v0", "v1", "v2", "v3", "v4", "v5"]
+    for s in sweeps:
+        kw = {}
+        for tok in s.split(","):
+            if tok.startswith("v"): kw["variant"] = int(tok[1:])
+            if tok.startswith("t"): kw["top_nodes"] = int(tok[1:])
+            if tok.startswith("f"): kw["fetch_threshold"] = int(tok[1:])
+            if tok.startswith("b"): kw["blocks_per_sm"] = int(tok[1:])
+        ctx.set_trace_config(**kw)
+        ms = median_ms(frame.trace_all)
+        out[s] = counted / ms / 1e3
+        print("%-16s %8.3f ms  %9.1f Mrays/s" % (s, ms, out[s]), flush=True)
+    ctx.set_trace_config()
+    frame.trace_all()
+    if O.have_ref_gpu():
+        # parity with the reference CUDA tracer on identical rays + BVH
+        for (b, _), r in zip(frame.batches, ref_res):
+            mine = b.getResults(); theirs = r[: b.getSize()].cpu().numpy().view(O.RESULT_DTYPE).reshape(-1)
+            if b.getNeedClosestHit():
+                same = mine["id"] == theirs["id"]
+                hit = same & (mine["id"] >= 0)
+                rel = np.abs(mine["t"][hit] - theirs["t"][hit]) / np.abs(theirs["t"][hit])
+                print("parity vs ref GPU: id agree %.6f, max rel t %.2e" % (same.mean(), rel.max(initial=0)))
+            else:
+                print("parity vs ref GPU (any-hit): hit/miss agree %.6f" % ((mine["id"] >= 0) == (theirs["id"] >= 0)).mean())
+    # SIMD efficiency
+    frame.tracer.collectStats = True
+    frame.trace_all()
+    st = frame.tracer.getStats()
+    frame.tracer.collectStats = False
+    print("SIMD eff (last batch): TRV %.1f%%  IST %.1f%%  fetches %d" % (
+        100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]), 100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"]))
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "explore_%s.json" % name), "w") as f:
+        json.dump(out, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()
