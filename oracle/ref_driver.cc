@@ -137,6 +137,22 @@ static double traceTimed(const BVH& bvh, RayBuffer& rb, int procs)
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+/* Bounded sample: every `stride`-th run of 64 consecutive slots (one 8x8 pixel block of the
+ * PixelTable order, PixelTable.cc:94-156), so the sample covers the whole frame evenly. */
+static void strideSample(RayBuffer& rb, int stride)
+{
+    if (stride <= 1) return;
+    S32 n = rb.getSize();
+    std::vector<Ray> keep;
+    for (S32 b = 0; b * 64 < n; b += stride)
+        for (S32 i = b * 64; i < n && i < b * 64 + 64; i++) keep.push_back(rb.getRayForSlot(i));
+    bool closest = rb.getNeedClosestHit();
+    rb.resize((S32)keep.size());
+    rb.setNeedClosestHit(closest);
+    for (S32 i = 0; i < (S32)keep.size(); i++) rb.setRay(i, keep[i]);
+    memcpy(rb.getRayBuffer_dev(), keep.data(), keep.size() * sizeof(Ray));
+}
+
 static void usage(void)
 {
     fprintf(stderr,
@@ -144,7 +160,7 @@ static void usage(void)
         "        [--camera-sig S | --camera-auto] [--size W H] [--camera-out F]\n"
         "        [--primary-out PREFIX]            rays via RayGen::primary -> PREFIX.rays/.slot2id\n"
         "        [--rays-in F [--any-hit]]         trace these instead of the primaries\n"
-        "        [--results-out F] [--procs P] [--limit N] [--repeat K]   BVH::trace, timed (one JSON line per repeat)\n"
+        "        [--results-out F] [--procs P] [--limit N] [--repeat K] [--budget-s T]   BVH::trace, timed (one JSON line per repeat)\n"
         "        [--ao-out PREFIX --samples S --max-dist D [--sort]]   RayGen::ao batches from the primaries\n"
         "        [--trace-secondary [--secondary-closest] [--secondary-results-out F]]  time BVH::trace on the first secondary batch\n"
         "        [--sort-in F --sort-out PREFIX]   RayBuffer::mortonSort\n");
@@ -158,6 +174,7 @@ int main(int argc, char** argv)
     std::string secResOut;
     float alpha = 1.0e-5f, maxDist = 0.0f;
     int W = 1024, H = 768, procs = 1, samples = 1, limit = -1, repeat = 1;
+    double budgetS = 0.0;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() -> const char* { if (i + 1 >= argc) usage(); return argv[++i]; };
@@ -176,6 +193,7 @@ int main(int argc, char** argv)
         else if (a == "--procs") procs = atoi(next());
         else if (a == "--limit") limit = atoi(next());
         else if (a == "--repeat") repeat = atoi(next());
+        else if (a == "--budget-s") budgetS = atof(next());      /* bound the total traced time by sampling the frame */
         else if (a == "--ao-out") aoOut = next();
         else if (a == "--samples") samples = atoi(next());
         else if (a == "--max-dist") maxDist = (float)atof(next());
@@ -281,6 +299,21 @@ int main(int argc, char** argv)
     }
 
     if (havePrimary && (!resOut.empty() || !aoOut.empty() || secTrace)) {
+        if (budgetS > 0.0 && raysIn.empty()) {
+            /* calibrate on a thin sample, then keep every stride-th 8x8 block of the frame */
+            RayBuffer probe(primary.getSize(), true);
+            for (S32 i = 0; i < primary.getSize(); i++) probe.setRay(i, primary.getRayForSlot(i));
+            int pstride = primary.getSize() / 64 / 1024; if (pstride < 1) pstride = 1;
+            strideSample(probe, pstride);
+            double ps = traceTimed(bvh, probe, procs);
+            double rate = probe.getSize() / ps;
+            double want = budgetS * rate / ((double)repeat * (secTrace ? 2 : 1));
+            int stride = (int)((double)primary.getSize() / want + 0.999999);
+            if (stride < 1) stride = 1;
+            strideSample(primary, stride);
+            fprintf(stderr, "ref_cpu: budget %.0fs, probe %.3f Mrays/s -> stride %d, %d rays per batch\n",
+                    budgetS, rate * 1e-6, stride, primary.getSize());
+        }
         S32 n = primary.getSize();
         double sec = 0.0;
         for (int rep = 0; rep < repeat; rep++) {
