@@ -68,6 +68,7 @@ _SIGNATURES = {
     "b2rt_morton_sort": (i32, [vp, vp, vp, vp, i64, vp, vp]),
     "b2rt_find_aabb": (i32, [vp, vp, i64, vp, vp]),
     "b2rt_morton_keys": (i32, [vp, vp, i64, vp, vp, vp]),
+    "b2rt_reorder_rays": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, vp]),
     "b2rt_count_hits": (i32, [vp, vp, i64, C.POINTER(i64), vp]),
     "b2rt_reconstruct": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]),
     "b2rt_pixel_table": (i32, [i32, i32, vp, vp]),

@@ -13,6 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libb2rt.so")
+REFABI_LIB = os.path.join(HERE, "libb2rt_refabi.so")      # the reference's launcher ABI on top of libb2rt (include/b2rt_refabi.h)
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -70,6 +71,11 @@ def build(force=False, verbose=False):
             log.append(_run([CXX] + HOST_FLAGS + ["-c", s, "-o", o], verbose))
     if force or not _newer(LIB, objs):
         log.append(_run([NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lpthread"], verbose))
+    refabi_src = os.path.join(CSRC, "host", "refabi.cpp")
+    if force or not _newer(REFABI_LIB, [refabi_src, LIB, os.path.join(INCLUDE, "b2rt_refabi.h")] + headers):
+        cuda_home = os.path.dirname(os.path.dirname(NVCC))
+        log.append(_run([CXX] + HOST_FLAGS + ["-I", os.path.join(cuda_home, "include"), "-shared", refabi_src, "-o", REFABI_LIB,
+                         "-L", HERE, "-lb2rt", "-L", os.path.join(cuda_home, "lib64"), "-lcudart", "-Wl,-rpath,$ORIGIN"], verbose))
     with open(os.path.join(OBJ, "build.log"), "a") as f:
         f.write("".join(log))
     return LIB

@@ -265,11 +265,11 @@ __global__ void __launch_bounds__(256) gatherWordKernel(const u64* __restrict__ 
 // reorderRaysKernel -- RayBufferKernels.cu:183-200
 __global__ void __launch_bounds__(256) reorderRaysKernel(const unsigned* __restrict__ sortedSlots, const float4* __restrict__ inRays,
                                                          const int32_t* __restrict__ inSlotToID, float4* outRays,
-                                                         int32_t* outIDToSlot, int32_t* outSlotToID, int n)
+                                                         int32_t* outIDToSlot, int32_t* outSlotToID, int n, int slotStride)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const unsigned oldSlot = sortedSlots[i];
+    const unsigned oldSlot = sortedSlots[(size_t)i * slotStride];   // stride 7: oldSlot of 28-byte MortonKey records
     const int id = inSlotToID[oldSlot];
     outRays[2 * (size_t)i] = __ldg(inRays + 2 * (size_t)oldSlot);
     outRays[2 * (size_t)i + 1] = __ldg(inRays + 2 * (size_t)oldSlot + 1);
@@ -421,9 +421,26 @@ int b2rt_morton_sort(b2rt_ctx* ctx, void* rays, int32_t* idToSlot, int32_t* slot
 
     B2RT_CUDA(ctx, cudaMemcpyAsync(oldRays, rays, (size_t)n * 32, cudaMemcpyDeviceToDevice, s));
     B2RT_CUDA(ctx, cudaMemcpyAsync(oldSlotToID, slotToID, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
-    reorderRaysKernel<<<g, 256, 0, s>>>(slotsCur, oldRays, oldSlotToID, static_cast<float4*>(rays), idToSlot, slotToID, n);
+    reorderRaysKernel<<<g, 256, 0, s>>>(slotsCur, oldRays, oldSlotToID, static_cast<float4*>(rays), idToSlot, slotToID, n, 1);
     B2RT_CHECK_LAUNCH(ctx, "reorderRaysKernel");
     if (aabbOut) return readAABB(ctx, aabbOut, s);
+    return B2RT_OK;
+}
+
+int b2rt_reorder_rays(b2rt_ctx* ctx, const void* keys, const void* inRays, const int32_t* inSlotToID, void* outRays,
+                      int32_t* outIDToSlot, int32_t* outSlotToID, int64_t n, void* stream)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (n < 0 || n > 0x7fffffff || (n && (!keys || !inRays || !inSlotToID || !outRays || !outIDToSlot || !outSlotToID)) ||
+        inRays == outRays)
+        return setError(ctx, B2RT_ERR_ARG, "b2rt_reorder_rays: bad arguments");
+    if (n == 0) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    reorderRaysKernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(static_cast<const unsigned*>(keys), static_cast<const float4*>(inRays),
+                                                                 inSlotToID, static_cast<float4*>(outRays), outIDToSlot, outSlotToID,
+                                                                 (int)n, 7);
+    B2RT_CHECK_LAUNCH(ctx, "reorderRaysKernel");
     return B2RT_OK;
 }
 

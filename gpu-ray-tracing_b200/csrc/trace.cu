@@ -291,8 +291,9 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
 
 
 // ---------------------------------------------------------------------------------------------
-// canonical work counters (b2rt_count_work): the scalar algorithm of oracle/b2rt_oracle.c's
-// b2o_trace_woop, one thread per ray, IEEE division -- counts, does not store hits
+// canonical work counters (b2rt_count_work): ordered stack traversal without speculation or
+// postponement (kepler_dynamic_fetch.cu:204-408 reduced to its scalar algorithm), one thread per
+// ray, IEEE division -- counts, does not store hits
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict__ rays, int numRays, int anyHit,
                                                        const float4* __restrict__ nodes, const float4* __restrict__ woop,

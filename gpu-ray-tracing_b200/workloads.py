@@ -18,7 +18,8 @@ from .host import BVH, CudaBVH, CudaTracer, Context, RayBuffer, RayGen, Scene, c
 
 CONFIGS = {
     "c1": dict(kind="blob", tris=144500, seed=20260102, size=(1024, 768), ray_type="primary", samples=1, sort=False),
-    "c2": dict(kind="interior", tris=350949, seed=20260103, size=(1024, 768), ray_type="diffuse", samples=1, sort=False),
+    "c2": dict(kind="interior", tris=350949, seed=20260103, size=(1024, 768), ray_type="diffuse", samples=1, sort=False,
+               with_primary=True),
     "c3": dict(kind="knot", tris=910348, seed=20260104, size=(1024, 768), ray_type="ao", samples=32, sort=True),
     "c4": dict(kind="strands", tris=6469561, seed=20260105, size=(1024, 768), ray_type="diffuse", samples=1, sort=False),
     "c5": dict(kind="knot", tris=910348, seed=20260104, size=(1024, 768), ray_type="diffuse", samples=86, sort=False,
@@ -88,6 +89,9 @@ class Frame:
             self.batches.append((self.primary, w * h))
             return
         self.tracer.traceBatch(self.primary)
+        if c.get("with_primary"):
+            # "primary + 1-bounce diffuse" (BASELINE.json configs[1]): the primary batch is a timed batch too
+            self.batches.append((self.primary, w * h))
         hits = countHits(self.primary.getResultBuffer_dev(), self.ctx)
         samples = c["samples"]
         far = scene.camera["far"]
@@ -124,7 +128,7 @@ class Frame:
                 sec.mortonSort(self.ctx)
             counted = int((sec.getRayBuffer_dev()[:, 7] >= 0).sum().item())     # degenerate rays have tmax = -1
             self.batches.append((sec, counted))
-        assert sum(b[1] for b in self.batches) == hits * samples               # Renderer.cc:221-238
+        assert sum(b[1] for b in self.batches if b[0] is not self.primary) == hits * samples   # Renderer.cc:221-238
 
     def counted_rays(self):
         return sum(b[1] for b in self.batches)

@@ -154,6 +154,12 @@ int b2rt_find_aabb(b2rt_ctx* ctx, const void* rays_dev, int64_t num_rays, float 
 int b2rt_morton_keys(b2rt_ctx* ctx, const void* rays_dev, int64_t num_rays, const float aabb[6],
                      void* keys_dev /* 28 B each: {int32 oldSlot; uint32 hash[6]} */, void* stream);
 
+/* replaces launch_reorderRaysKernel (RayBufferKernels.hh:81-91,116; RayBufferKernels.cu:183-200): gather rays by
+ * the oldSlot of sorted 28-byte MortonKey records and rebuild both id maps.  Out of place. */
+int b2rt_reorder_rays(b2rt_ctx* ctx, const void* keys_dev, const void* in_rays_dev,
+                      const int32_t* in_slot_to_id_dev, void* out_rays_dev, int32_t* out_id_to_slot_dev,
+                      int32_t* out_slot_to_id_dev, int64_t num_rays, void* stream);
+
 /* ---- hit count / reconstruction --------------------------------------------------------- */
 /* replaces launch_countHitsKernel (cuda/RendererKernels.hh:77-92, RendererKernels.cu:112-162):
  * number of results with id >= 0.  Synchronous. */

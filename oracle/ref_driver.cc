@@ -10,11 +10,13 @@
  * CudaBVH::createCompact + woopifyTri, CudaBVH::serialize (bvhcache format), CameraControls,
  * PixelTable, RayGen::primary / RayGen::ao host logic (batching, rand() seed), RayBuffer
  * (id<->slot maps, mortonSort with FW::sort), BVH::trace.
- * What is ours: the CUDA-only pieces.  The reference's kernels cannot run without a GPU, so the
- * C-linkage launchers its host code calls (launch_rayGenPrimaryKernel ... launch_reorderRaysKernel,
- * RayGenKernels.hh:107-111, RayBufferKernels.hh:112-117) are bound here to the CPU restatement
- * in b2rt_oracle.c; cudaMalloc/cudaMemcpy/cudaFree are bound to malloc/memcpy/free (stubs.c),
- * so "device" pointers are host pointers.
+ * The reference's ray-generation, Morton-key, reorder and reconstruct KERNELS run too: their .cu
+ * files are compiled as host C++ with gpu_ref/host_emul.h and every emulated thread executes the
+ * reference's own kernel body (launch_rayGenPrimaryKernel ... launch_reorderRaysKernel,
+ * RayGenKernels.hh:107-111, RayBufferKernels.hh:112-117, RendererKernels.hh:88-92).
+ * What is ours: launch_findAABBKernel (a block-cooperative reduction a serial loop cannot emulate)
+ * is bound to b2rt_oracle.c; cudaMalloc/cudaMemcpy/cudaFree are bound to malloc/memcpy/free
+ * (stubs.c), so "device" pointers are host pointers.
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -43,31 +45,14 @@
 
 using namespace FW;
 
-/* ---- CPU bindings for the launchers the reference host code calls ---- */
-extern "C" void launch_rayGenPrimaryKernel(S32, struct RayGenPrimaryInput& in)
-{
-    b2o_raygen_primary(in.origin.getPtr(), in.nscreenToWorld.getPtr(), in.w, in.h, in.maxDist,
-                       in.indexToPixel, (b2o_ray*)in.rays, in.idToSlot, in.slotToID);
-}
-extern "C" void launch_rayGenAOKernel(S32, struct RayGenAOInput& in)
-{
-    b2o_raygen_ao(in.firstInputSlot, in.numInputRays, in.numSamples, in.maxDist, in.randomSeed,
-                  (const b2o_ray*)in.inRays, (const b2o_result*)in.inResults, (const float*)in.normals,
-                  (b2o_ray*)in.outRays, in.outIDToSlot, in.outSlotToID);
-}
+/* ---- launchers the reference host code calls ----
+ * launch_rayGenPrimaryKernel / launch_rayGenAOKernel / launch_genMortonKeysKernel /
+ * launch_reorderRaysKernel / launch_reconstructKernel are the REFERENCE'S OWN (RayGenKernels.cu,
+ * RayBufferKernels.cu, RendererKernels.cu compiled as host C++, kernel bodies run serially: see
+ * gpu_ref/host_emul.h).  Only the two block-cooperative reductions are bound to the restatement. */
 extern "C" void launch_findAABBKernel(S32, const Vec2i&, struct FindAABBInput& in, struct FindAABBOutput& out)
 {
     b2o_find_aabb((const b2o_ray*)in.inRays, in.numRays, out.aabbLo.getPtr(), out.aabbHi.getPtr());
-}
-extern "C" void launch_genMortonKeysKernel(S32, const Vec2i&, struct GenMortonKeysInput& in)
-{
-    b2o_morton_keys((const b2o_ray*)in.inRays, in.numRays, in.aabbLo.getPtr(), in.aabbHi.getPtr(),
-                    (b2o_mortonkey*)in.outKeys);
-}
-extern "C" void launch_reorderRaysKernel(S32, struct ReorderRaysInput& in)
-{
-    b2o_reorder_rays(in.numRays, (const b2o_mortonkey*)in.inKeys, (const b2o_ray*)in.inRays,
-                     in.inSlotToID, (b2o_ray*)in.outRays, in.outIDToSlot, in.outSlotToID);
 }
 
 /* ---- helpers ---- */
