@@ -101,3 +101,38 @@ def test_no_bvh_and_wrong_layout_fail(b2rt, ctx):
     rb = b2rt.RayBuffer(4)
     with pytest.raises(RuntimeError, match="No BVH"):
         tracer.traceBatch(rb)
+
+
+def test_reference_launcher_abi(b2rt, oracle, ctx):
+    """libb2rt_refabi.so: bind_CudaBVHTexture + launch_tracingKernel + launch_countHitsKernel with the reference's
+    argument lists (CudaTracerKernels.hh:42-52, RendererKernels.hh:88-92) give the same hit records as b2rt_trace."""
+    import ctypes as C
+    import os
+    import torch
+    lib = C.CDLL(os.path.join(os.path.dirname(b2rt.LIB_PATH), "libb2rt_refabi.so"))
+    lib.launch_tracingKernel.restype = C.c_float
+    lib.launch_tracingKernel.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_bool] + [C.c_void_p] * 10
+    lib.bind_CudaBVHTexture.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+    scene = b2rt.Scene.generate("interior", 20000, 21)
+    bvh = b2rt.BVH(scene)
+    cb = b2rt.CudaBVH(bvh)
+    rays = _primary_rays(b2rt, oracle, scene, 128, 96)
+    rb = b2rt.RayBuffer()
+    rb.setRays(rays)
+    n, w, t = cb.getNodeBuffer_dev(), cb.getTriWoopBuffer_dev(), cb.getTriIndexBuffer_dev()
+    torch.cuda.set_device(0)
+    lib.bind_CudaBVHTexture(n.data_ptr(), n.numel() * 4, w.data_ptr(), w.numel() * 4, t.data_ptr(), t.numel() * 4)
+    res = torch.zeros((len(rays), 4), dtype=torch.int32, device="cuda")
+    block = (C.c_int * 2)(32, 4)
+    ms = lib.launch_tracingKernel(23040, block, len(rays), False, rb.m_rays.data_ptr(), res.data_ptr(), n.data_ptr(), n.data_ptr(),
+                                  n.data_ptr(), n.data_ptr(), w.data_ptr(), w.data_ptr(), w.data_ptr(), t.data_ptr())
+    assert ms > 0.0
+    got = res.cpu().numpy().view(oracle.RESULT_DTYPE).reshape(-1)
+    _check_closest(oracle, bvh.arrays(), rays, got)
+
+    class CountHitsInput(C.Structure):
+        _fields_ = [("numRays", C.c_int32), ("rayResults", C.c_void_p), ("raysPerThread", C.c_int32)]
+    inp = CountHitsInput(len(rays), res.data_ptr(), 32)
+    lib.launch_countHitsKernel.restype = C.c_int32
+    hits = lib.launch_countHitsKernel(C.c_int32(0), block, C.byref(inp))
+    assert hits == int((got["id"] >= 0).sum())
