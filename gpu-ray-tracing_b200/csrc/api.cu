@@ -41,7 +41,7 @@ static int ensureStage(b2rt_ctx* ctx, size_t bytes)
 }
 
 // How many leading nodes of the private copy are ordered "most likely visited first".
-constexpr int kMaxTopNodes = 2048;
+constexpr int kMaxTopNodes = 4096;
 
 // Re-lay the node array: the kMaxTopNodes nodes with the largest boxes (a greedy descent from the
 // root by surface area, i.e. by SAH visit probability) come first, the rest keep their order.

@@ -40,7 +40,7 @@ struct b2rt_ctx {
     int topNodesAvail = 0;     // how many leading nodes are in breadth-first order
     bool hasBvh = false;
 
-    b2rt_trace_config cfg = { -1, -1, -1, 0 };
+    b2rt_trace_config cfg = { -1, -1, -1, -1 };
 
     int* warpCounter = nullptr;                 // work counter for persistent warps
     unsigned long long* statsDev = nullptr;     // 8 counters for the instrumented kernel
@@ -90,6 +90,19 @@ __device__ __forceinline__ float rcp_approx(float x)
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
+}
+// shared-memory loads through a 32-bit shared-window address (read-only data staged before a barrier)
+__device__ __forceinline__ float4 lds128(unsigned addr)
+{
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ int2 lds64i(unsigned addr)
+{
+    int2 v;
+    asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
 }
 // sm_100a three-input float min/max (SASS FMNMX3)
 __device__ __forceinline__ float fmin3(float a, float b, float c)

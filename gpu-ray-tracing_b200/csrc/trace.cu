@@ -42,15 +42,31 @@ template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MI
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
     extern __shared__ float4 s_dyn[];
-    float4* s_top = s_dyn;
-    int* s_stack = reinterpret_cast<int*>(s_dyn + p.topF4) + threadIdx.x;   // slot k at s_stack[k * BLOCK]
-
-    // Stage the top of the tree (same bytes for every CTA; L2 serves all but the first).
-    for (int i = threadIdx.x; i < p.topF4; i += BLOCK) s_top[i] = ldg4(p.nodes + i);
+    // Shared memory: [stack: STACK_SMEM x BLOCK ints][top nodes, structure-of-arrays].
+    // The top `topNodes` nodes of the re-laid array are staged as four planes -- plane 0/1/2 hold the
+    // node's first three float4s (16 B per node), plane 3 its two child indices (8 B per node) -- so
+    // lanes that read DIFFERENT nodes in one LDS.128 hit banks (node mod 8) instead of all starting
+    // at bank 0 or 16 as an array-of-64-byte-structs would (ncu: 8.6 M excessive shared wavefronts
+    // per launch in the AoS version, profiles/r01_ncu_trace_c2.md).
+    int* s_stack = reinterpret_cast<int*>(s_dyn) + threadIdx.x;              // slot k at s_stack[k * BLOCK]
+    const int topF4 = p.topF4;
+    const int topNodes = topF4 >> 2;
+    float4* s_plane = s_dyn + (STACK_SMEM * BLOCK) / 4;
+    {
+        int2* s_child = reinterpret_cast<int2*>(s_plane + 3 * topNodes);
+        for (int i = threadIdx.x; i < topF4; i += BLOCK) {
+            const float4 v = ldg4(p.nodes + i);
+            const int node = i >> 2, k = i & 3;
+            if (k < 3) s_plane[k * topNodes + node] = v;
+            else s_child[node] = make_int2(__float_as_int(v.x), __float_as_int(v.y));
+        }
+    }
     __syncthreads();
+    unsigned sTop = (unsigned)__cvta_generic_to_shared(s_plane);              // 32-bit shared address of plane 0
+    asm volatile("mov.u32 %0, %0;" : "+r"(sTop));      // opaque: keep it in a register instead of re-deriving it per node
+    const unsigned planeBytes = (unsigned)topNodes * 16u;
 
     const int lane = threadIdx.x & 31;
-    const int topF4 = p.topF4;
     int lstack[kLocalStack];            // spill area, touched only when a stack outgrows STACK_SMEM
 
     // Per-ray state.
@@ -123,11 +139,19 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             // inner nodes, until every participating lane holds a postponed leaf
             while ((unsigned)nodeAddr < (unsigned)kSentinel) {
                 if (STATS) { const unsigned am = __activemask(); stNodeLanes++; if (lane == __ffs(am) - 1) stNodeIters++; }
-                const float4* np = (nodeAddr < topF4) ? (s_top + nodeAddr) : (p.nodes + nodeAddr);
-                float4 n0xy, n1xy, nz, cn;
-                if (nodeAddr < topF4) { n0xy = np[0]; n1xy = np[1]; nz = np[2]; cn = np[3]; }
-                else { n0xy = ldg4(np); n1xy = ldg4(np + 1); nz = ldg4(np + 2); cn = ldg4(np + 3); }
-                int c0 = __float_as_int(cn.x), c1 = __float_as_int(cn.y);
+                float4 n0xy, n1xy, nz;
+                int c0, c1;
+                if (nodeAddr < topF4) {
+                    const unsigned a = sTop + ((unsigned)nodeAddr << 2);      // node index * 16 bytes
+                    n0xy = lds128(a); n1xy = lds128(a + planeBytes); nz = lds128(a + 2u * planeBytes);
+                    const int2 ch = lds64i(sTop + 3u * planeBytes + ((unsigned)nodeAddr << 1));
+                    c0 = ch.x; c1 = ch.y;
+                } else {
+                    const float4* np = p.nodes + nodeAddr;
+                    n0xy = ldg4(np); n1xy = ldg4(np + 1); nz = ldg4(np + 2);
+                    const int2 ch = __ldg(reinterpret_cast<const int2*>(np + 3));
+                    c0 = ch.x; c1 = ch.y;
+                }
 
                 const float c0lox = __fmaf_rn(n0xy.x, idirx, -oodx), c0hix = __fmaf_rn(n0xy.y, idirx, -oodx);
                 const float c0loy = __fmaf_rn(n0xy.z, idiry, -oody), c0hiy = __fmaf_rn(n0xy.w, idiry, -oody);
@@ -224,14 +248,15 @@ template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MI
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
     auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS>;
-    int topNodes = ctx->cfg.top_nodes < 0 ? 512 : ctx->cfg.top_nodes;
+    int topNodes = ctx->cfg.top_nodes < 0 ? (BLOCK >= 1024 ? 2048 : 512) : ctx->cfg.top_nodes;
     if (topNodes > ctx->topNodesAvail) topNodes = ctx->topNodesAvail;
     size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int);
     // keep MIN_BLOCKS CTAs resident inside the 227 KB a CTA can opt into
     const size_t smemBudget = (size_t)(227 * 1024) / MIN_BLOCKS - 1024;
-    while (topNodes > 0 && (size_t)topNodes * 64 + stackBytes > smemBudget) topNodes /= 2;
+    topNodes &= ~7;                                  // planes stay 128-byte aligned
+    while (topNodes > 0 && (size_t)topNodes * 56 + stackBytes > smemBudget) topNodes = (topNodes / 2) & ~7;
     p.topF4 = topNodes * 4;
-    size_t smem = (size_t)p.topF4 * sizeof(float4) + stackBytes;
+    size_t smem = (size_t)topNodes * 56 + stackBytes;
     B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int blocksPerSm = 0;
     B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, smem));
@@ -278,7 +303,14 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 8 * sizeof(unsigned long long), stream));
-    switch (ctx->cfg.variant) {
+    int variant = ctx->cfg.variant;
+    if (variant < 0) {
+        // measured on B200 (profiles/r01_explore_*_v2.log): one 1024-thread CTA per SM with a 2048-node shared top of
+        // the tree wins on frame-sized batches (shorter tail, more node visits served from shared memory); four
+        // 256-thread CTAs win on multi-million-ray batches
+        variant = (numRays <= (4 << 20)) ? 6 : 1;
+    }
+    switch (variant) {
     default:
     case 0: return launchFlags<12, 256, 5>(ctx, p, flags, stream);   // <= 48 regs, 40 warps/SM
     case 1: return launchFlags<12, 256, 4>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM
@@ -286,6 +318,8 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     case 3: return launchFlags<16, 128, 8>(ctx, p, flags, stream);   // small CTAs
     case 4: return launchFlags<8, 512, 3>(ctx, p, flags, stream);    // big CTAs, 48 warps/SM (<= 40 regs)
     case 5: return launchFlags<12, 256, 6>(ctx, p, flags, stream);   // <= 40 regs, 48 warps/SM
+    case 6: return launchFlags<12, 1024, 1>(ctx, p, flags, stream);  // one CTA per SM: one big shared top-of-tree
+    case 7: return launchFlags<12, 512, 2>(ctx, p, flags, stream);   // two CTAs per SM, <= 64 regs
     }
 }
 

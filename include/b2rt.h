@@ -75,7 +75,7 @@ typedef struct {
     int fetch_threshold;        /* refill dead lanes when fewer than this are alive
                                    (kepler_dynamic_fetch.cu:48 uses 20); -1 = default */
     int blocks_per_sm;          /* persistent CTAs per SM; -1 = from occupancy */
-    int variant;                /* kernel variant id, 0 = default */
+    int variant;                /* kernel variant id; -1 = chosen from the batch size */
 } b2rt_trace_config;
 
 /* ---- context ---------------------------------------------------------------------------- */
