@@ -80,6 +80,9 @@ _SIGNATURES = {
     "b2rt_bvh_save": (i32, [vp, C.c_char_p]),
     "b2rt_bvh_load": (i32, [C.c_char_p, C.POINTER(vp)]),
     "b2rt_tri_normals": (i32, [vp, vp, i32, vp]),
+    "b2rt_wide_build": (i32, [vp, sz, vp, sz, vp, sz, C.POINTER(vp)]),
+    "b2rt_wide_free": (None, [vp]),
+    "b2rt_wide_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), vp]),
     "b2rt_scene_generate": (i32, [i32, i32, C.c_uint64, C.POINTER(vp)]),
     "b2rt_scene_free": (None, [vp]),
     "b2rt_scene_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(i32), C.POINTER(vp), C.POINTER(i32)]),

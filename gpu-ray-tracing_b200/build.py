@@ -26,12 +26,13 @@ NVCC_COMMON = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "
 # spells out every FMA itself.
 CUDA_SOURCES = [
     ("trace.cu", ["-Xptxas", "-v"]),
+    ("trace_wide.cu", ["-Xptxas", "-v"]),
     ("api.cu", []),
     ("raygen.cu", ["-fmad=false"]),
     ("raysort.cu", ["-fmad=false"]),
     ("misc.cu", ["-fmad=false"]),
 ]
-HOST_SOURCES = ["host/bvh_builder.cpp", "host/scenegen.cpp", "host/host_util.cpp"]
+HOST_SOURCES = ["host/bvh_builder.cpp", "host/scenegen.cpp", "host/host_util.cpp", "host/wide_bvh.cpp"]
 HOST_FLAGS = ["-O2", "-ffp-contract=off", "-fPIC", "-std=c++17", "-pthread", "-Wall", "-I", INCLUDE]
 
 
@@ -54,7 +55,7 @@ def _run(cmd, verbose):
 
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
-    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(INCLUDE, "b2rt.h"), os.path.abspath(__file__)]
+    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "wide_bvh.h"), os.path.join(INCLUDE, "b2rt.h"), os.path.abspath(__file__)]
     objs = []
     log = []
     for src, extra in CUDA_SOURCES:

@@ -1,5 +1,6 @@
 // api.cu -- context, BVH upload and the trace entry points of the C ABI (include/b2rt.h).
 #include "common.cuh"
+#include "wide_bvh.h"
 
 #include <stdarg.h>
 
@@ -89,6 +90,42 @@ static void relayoutNodes(const std::vector<float>& in, std::vector<float>& out,
     }
 }
 
+static void freeWide(b2rt_ctx* ctx)
+{
+    cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
+    ctx->wideNodes = nullptr; ctx->wideWoop = nullptr; ctx->wideTriIndex = nullptr;
+    ctx->wideNumNodes = ctx->wideNumTris = 0;
+    ctx->hasWide = false;
+}
+
+// Collapse the private Compact2 copy (node order is irrelevant to the collapse; the root is node 0 in both orders)
+// into the 8-wide compressed form.  One-off host work per BVH: D2H of the three arrays, collapse, H2D.
+int ensureWide(b2rt_ctx* ctx)
+{
+    if (ctx->hasWide) return B2RT_OK;
+    if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
+    std::vector<float> nodes(ctx->nodeBytes / 4), woop(ctx->woopBytes / 4);
+    std::vector<int32_t> tri(ctx->triIndexBytes / 4);
+    B2RT_CUDA(ctx, cudaMemcpy(nodes.data(), ctx->nodes, ctx->nodeBytes, cudaMemcpyDeviceToHost));
+    if (ctx->woopBytes) B2RT_CUDA(ctx, cudaMemcpy(woop.data(), ctx->woop, ctx->woopBytes, cudaMemcpyDeviceToHost));
+    if (ctx->triIndexBytes) B2RT_CUDA(ctx, cudaMemcpy(tri.data(), ctx->triIndex, ctx->triIndexBytes, cudaMemcpyDeviceToHost));
+    Wide8 w;
+    const char* err = "";
+    if (!buildWide8(nodes.data(), nodes.size() / 16, woop.data(), tri.data(), woop.size() / 4, w, &err))
+        return setError(ctx, B2RT_ERR_ARG, "wide BVH build failed: %s", err);
+    freeWide(ctx);
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->wideNodes, w.nodes.size() * 4));
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->wideWoop, w.woop.size() * 4));
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->wideTriIndex, w.triIndex.size() * 4 + 16));
+    B2RT_CUDA(ctx, cudaMemcpy(ctx->wideNodes, w.nodes.data(), w.nodes.size() * 4, cudaMemcpyHostToDevice));
+    B2RT_CUDA(ctx, cudaMemcpy(ctx->wideWoop, w.woop.data(), w.woop.size() * 4, cudaMemcpyHostToDevice));
+    if (!w.triIndex.empty())
+        B2RT_CUDA(ctx, cudaMemcpy(ctx->wideTriIndex, w.triIndex.data(), w.triIndex.size() * 4, cudaMemcpyHostToDevice));
+    ctx->wideNumNodes = w.numNodes; ctx->wideNumTris = w.numTris;
+    ctx->hasWide = true;
+    return B2RT_OK;
+}
+
 }  // namespace b2rt
 
 using namespace b2rt;
@@ -136,6 +173,7 @@ void b2rt_destroy(b2rt_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaFree(ctx->nodes); cudaFree(ctx->woop); cudaFree(ctx->triIndex);
+    cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
     cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch); cudaFree(ctx->stage);
     cudaFree(ctx->aabbDev); cudaFree(ctx->countDev);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -174,6 +212,7 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaFree(ctx->nodes); cudaFree(ctx->woop); cudaFree(ctx->triIndex);
     ctx->nodes = nullptr; ctx->woop = nullptr; ctx->triIndex = nullptr; ctx->hasBvh = false;
+    freeWide(ctx);
 
     // nodes: host round trip for the re-layout (one-off, at most tens of MB)
     std::vector<float> in(nodeBytes / 4), out;

@@ -40,6 +40,11 @@ struct b2rt_ctx {
     int topNodesAvail = 0;     // how many leading nodes are in breadth-first order
     bool hasBvh = false;
 
+    // second private form: 8-wide compressed nodes + re-packed Woop rows (wide_bvh.h), built on first use
+    float4* wideNodes = nullptr; float4* wideWoop = nullptr; int32_t* wideTriIndex = nullptr;
+    int wideNumNodes = 0, wideNumTris = 0;
+    bool hasWide = false;
+
     b2rt_trace_config cfg = { -1, -1, -1, -1 };
 
     int* warpCounter = nullptr;                 // work counter for persistent warps
@@ -79,6 +84,10 @@ extern std::string g_createError;
 // kernels' launchers (defined in the .cu files)
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
                 cudaStream_t stream);
+
+int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
+                    cudaStream_t stream);
+int ensureWide(b2rt_ctx* ctx);      // builds the wide form from the private Compact2 copy if it is not there yet
 
 int countWork(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, cudaStream_t stream);
 

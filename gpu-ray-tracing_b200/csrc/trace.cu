@@ -310,6 +310,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // 256-thread CTAs win on multi-million-ray batches
         variant = (numRays <= (4 << 20)) ? 6 : 1;
     }
+    if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {
     default:
     case 0: return launchFlags<12, 256, 5>(ctx, p, flags, stream);   // <= 48 regs, 40 warps/SM

@@ -1,0 +1,276 @@
+// trace_wide.cu -- closest-hit / any-hit traversal of the PRIVATE 8-wide compressed form of the
+// caller's Compact2 BVH (wide_bvh.h; built by host/wide_bvh.cpp inside the context).
+//
+// Why it exists: ncu on the binary kernel (profiles/r01_ncu_trace_c2.md) shows the LSU data pipe at
+// 87 % of peak while active and `long_scoreboard` as the top stall -- every node visit costs each lane
+// four 16-byte loads from a different 64-byte record.  An 8-wide node with 8-bit child boxes is 80
+// bytes for EIGHT boxes, and a ray visits ~0.4x as many of them, so both the bytes through L1 and the
+// number of dependent fetches per ray drop by more than half.  Same contract as trace.cu: persistent
+// warps with a ballot-aggregated atomic ray fetch and dynamic refill, Woop test on the caller's own
+// rows (so t, u, v are bit-identical to the binary path), one result store per ray.
+//
+// Traversal state per lane (after Ylitie et al., HPG 2017):
+//   G = (base index of a group of sibling nodes, hits in bits 31..24 | imask in bits 7..0)
+//   T = (base index of a group of triangles,     hits in bits 23..0)
+// A node step pops the highest hit bit of G -- bit position = 24 + (slot XOR ray octant), so siblings
+// come out front to back -- pushes the rest of G, tests the eight child boxes of that node and forms
+// the next G and T from the resulting 32-bit hit mask.
+#include "common.cuh"
+
+namespace b2rt {
+
+struct WideParams {
+    const float4* __restrict__ rays;
+    int4* __restrict__ results;
+    const float4* __restrict__ nodes;       // 5 float4 per node
+    const float4* __restrict__ woop;        // 3 float4 per triangle
+    const int* __restrict__ triIndex;       // 1 per triangle
+    int numRays;
+    int fetchThreshold;
+    int* warpCounter;
+    unsigned long long* stats;
+};
+
+constexpr int kWideStack = 48;          // group entries; the collapsed tree is at most as deep as the binary one (<= 64, typ. < 12)
+constexpr unsigned kFullMask = 0xffffffffu;
+
+// byte j of `word` as the float 1 + byte * 2^-15 (exact): one PRMT, no integer-to-float conversion
+template <int J>
+__device__ __forceinline__ float byteToUnitFloat(unsigned word)
+{
+    return __uint_as_float(__byte_perm(word, 0x3F800000u, 0x7604u | (J << 4)));
+}
+
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS>
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
+{
+    const int lane = threadIdx.x & 31;
+    uint2 stack[kWideStack];
+
+    float origx = 0, origy = 0, origz = 0, dirx = 0, diry = 0, dirz = 0;
+    float idirx = 0, idiry = 0, idirz = 0, tmin = 0, hitT = 0, hitU = 0, hitV = 0;
+    int hitIndex = -1, rayidx = -1, sp = 0;
+    unsigned octinv4 = 0;
+    uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
+    bool active = false;
+    bool poolEmpty = false;
+    unsigned long long stNodeIters = 0, stNodeLanes = 0, stTriIters = 0, stTriLanes = 0, stFetches = 0;
+
+    while (true) {
+        __syncwarp();
+        // ---- store finished rays, refill (same scheme as trace.cu) ----------------------------
+        if (!active && rayidx >= 0) {
+            const int id = (hitIndex < 0) ? -1 : __ldg(p.triIndex + hitIndex);
+            if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
+            else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
+            rayidx = -1;
+        }
+        const unsigned maskT = __ballot_sync(kFullMask, !active);
+        if (maskT != 0 && !poolEmpty) {
+            const int numT = __popc(maskT);
+            const int leader = __ffs(maskT) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(p.warpCounter, numT);
+            base = __shfl_sync(kFullMask, base, leader);
+            if (STATS && lane == leader) stFetches++;
+            poolEmpty = (base + numT >= p.numRays);
+            if (!active) {
+                const int idx = base + __popc(maskT & ((1u << lane) - 1u));
+                if (idx < p.numRays) {
+                    rayidx = idx;
+                    const float4 o = ldg4(p.rays + 2 * (size_t)idx);
+                    const float4 d = ldg4(p.rays + 2 * (size_t)idx + 1);
+                    origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
+                    dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
+                    const float ooeps = 8.271806125530277e-25f;    // 2^-80 (kepler_dynamic_fetch.cu:134-137)
+                    idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+                    idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+                    idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+                    // bit set <=> the ray travels towards + on that axis; replicated into four bytes
+                    octinv4 = ((idirx < 0.0f ? 0u : 4u) | (idiry < 0.0f ? 0u : 2u) | (idirz < 0.0f ? 0u : 1u)) * 0x01010101u;
+                    G = make_uint2(0u, 0x80000000u);               // the root, as a group of one
+                    T = make_uint2(0u, 0u);
+                    sp = 0; hitIndex = -1;
+                    // a degenerate ray (tmax < tmin, RayGenKernels.cu:223) can hit nothing: finish it here
+                    active = !(hitT < tmin);
+                }
+            }
+        }
+        if (__ballot_sync(kFullMask, active) == 0) {
+            if (__ballot_sync(kFullMask, rayidx >= 0) == 0) break;  // nothing in flight, nothing to store: the pool is empty
+            continue;                                               // only degenerate rays were fetched: store them, fetch again
+        }
+        const int threshold = poolEmpty ? 0 : p.fetchThreshold;
+
+        while (active) {
+            // ---- node step ----------------------------------------------------------------------
+            if (G.y > 0x00FFFFFFu) {
+                if (STATS) { const unsigned am = __activemask(); stNodeLanes++; if (lane == __ffs(am) - 1) stNodeIters++; }
+                const unsigned bit = 31u - __clz(G.y);
+                G.y &= ~(1u << bit);
+                if (G.y > 0x00FFFFFFu) stack[sp++] = G;
+                const unsigned slot = (bit - 24u) ^ (octinv4 & 7u);
+                const unsigned rel = __popc(G.y & ((1u << slot) - 1u) & 0xFFu);
+                const float4* n = p.nodes + (size_t)(G.x + rel) * 5;
+                const float4 q0 = ldg4(n), q1 = ldg4(n + 1), q2 = ldg4(n + 2), q3 = ldg4(n + 3), q4 = ldg4(n + 4);
+
+                const unsigned ew = __float_as_uint(q0.w);
+                const float ax = __uint_as_float((ew & 0xFFu) << 23) * idirx;
+                const float ay = __uint_as_float((ew & 0xFF00u) << 15) * idiry;
+                const float az = __uint_as_float((ew & 0xFF0000u) << 7) * idirz;
+                const float bx = __fmaf_rn(q0.x - origx, idirx, -ax);
+                const float by = __fmaf_rn(q0.y - origy, idiry, -ay);
+                const float bz = __fmaf_rn(q0.z - origz, idirz, -az);
+                // entry / exit planes by ray direction: no per-child min/max over the two planes of an axis
+                const bool nx = idirx < 0.0f, ny = idiry < 0.0f, nz = idirz < 0.0f;     // idir is never zero (2^-80 clamp keeps the sign)
+                unsigned hitmask = 0;
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const unsigned loX = __float_as_uint(h ? q2.y : q2.x), loY = __float_as_uint(h ? q2.w : q2.z);
+                    const unsigned loZ = __float_as_uint(h ? q3.y : q3.x), hiX = __float_as_uint(h ? q3.w : q3.z);
+                    const unsigned hiY = __float_as_uint(h ? q4.y : q4.x), hiZ = __float_as_uint(h ? q4.w : q4.z);
+                    const unsigned nearX = nx ? hiX : loX, farX = nx ? loX : hiX;
+                    const unsigned nearY = ny ? hiY : loY, farY = ny ? loY : hiY;
+                    const unsigned nearZ = nz ? hiZ : loZ, farZ = nz ? loZ : hiZ;
+                    const unsigned meta4 = __float_as_uint(h ? q1.w : q1.z);
+                    const unsigned isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                    const unsigned innerMask4 = (isInner4 >> 4) * 0xFFu;
+                    const unsigned bitIndex4 = (meta4 ^ (octinv4 & innerMask4)) & 0x1F1F1F1Fu;
+                    const unsigned childBits4 = (meta4 >> 5) & 0x07070707u;
+#define B2RT_WIDE_CHILD(J)                                                                                          \
+                    {                                                                                               \
+                        const float t0x = __fmaf_rn(byteToUnitFloat<J>(nearX), ax, bx);                           \
+                        const float t0y = __fmaf_rn(byteToUnitFloat<J>(nearY), ay, by);                           \
+                        const float t0z = __fmaf_rn(byteToUnitFloat<J>(nearZ), az, bz);                           \
+                        const float t1x = __fmaf_rn(byteToUnitFloat<J>(farX), ax, bx);                            \
+                        const float t1y = __fmaf_rn(byteToUnitFloat<J>(farY), ay, by);                            \
+                        const float t1z = __fmaf_rn(byteToUnitFloat<J>(farZ), az, bz);                            \
+                        const float cmin = fmax3(t0x, t0y, fmaxf(t0z, tmin));                                      \
+                        const float cmax = fmin3(t1x, t1y, fminf(t1z, hitT));                                      \
+                        if (cmin <= cmax) hitmask |= ((childBits4 >> (8 * J)) & 0xFFu) << ((bitIndex4 >> (8 * J)) & 0xFFu); \
+                    }
+                    B2RT_WIDE_CHILD(0) B2RT_WIDE_CHILD(1) B2RT_WIDE_CHILD(2) B2RT_WIDE_CHILD(3)
+#undef B2RT_WIDE_CHILD
+                }
+                G = make_uint2(__float_as_uint(q1.x), (hitmask & 0xFF000000u) | (ew >> 24));
+                T = make_uint2(__float_as_uint(q1.y), hitmask & 0x00FFFFFFu);
+            } else {
+                T = G;                                              // a postponed triangle group came off the stack
+                G = make_uint2(0u, 0u);
+            }
+
+            // ---- triangles of this node ---------------------------------------------------------
+            while (T.y != 0u) {
+                if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
+                const int k = __ffs(T.y) - 1;
+                T.y &= T.y - 1u;
+                const int tri = (int)T.x + k;
+                const float4* w = p.woop + (size_t)tri * 3;
+                const float4 v00 = ldg4(w), v11 = ldg4(w + 1), v22 = ldg4(w + 2);
+                // Woop test, same operation order as trace.cu (kepler_dynamic_fetch.cu:336-379)
+                const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
+                const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
+                const float t = __fmul_rn(Oz, invDz);
+                if (t > tmin && t < hitT) {
+                    const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
+                    const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
+                    const float u = __fmaf_rn(t, Dx, Ox);
+                    if (u >= 0.0f) {
+                        const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
+                        const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
+                        const float v = __fmaf_rn(t, Dy, Oy);
+                        if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                            hitT = t; hitIndex = tri;
+                            if (BARY) { hitU = u; hitV = v; }
+                            if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; }
+                        }
+                    }
+                }
+            }
+
+            // ---- next group ---------------------------------------------------------------------
+            if (G.y <= 0x00FFFFFFu) {
+                if (sp == 0) { active = false; break; }
+                G = stack[--sp];
+            }
+            if (__popc(__activemask()) < threshold) break;          // dynamic fetch: refill the idle lanes
+        }
+    }
+
+    if (STATS) {
+        for (int o = 16; o > 0; o >>= 1) {
+            stNodeIters += __shfl_xor_sync(kFullMask, stNodeIters, o);
+            stNodeLanes += __shfl_xor_sync(kFullMask, stNodeLanes, o);
+            stTriIters += __shfl_xor_sync(kFullMask, stTriIters, o);
+            stTriLanes += __shfl_xor_sync(kFullMask, stTriLanes, o);
+            stFetches += __shfl_xor_sync(kFullMask, stFetches, o);
+        }
+        if (lane == 0) {
+            atomicAdd(p.stats + 0, stNodeIters); atomicAdd(p.stats + 1, stNodeLanes);
+            atomicAdd(p.stats + 2, stTriIters);  atomicAdd(p.stats + 3, stTriLanes);
+            atomicAdd(p.stats + 4, stFetches);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// launcher
+// ---------------------------------------------------------------------------------------------
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS>
+static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
+{
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS>;
+    int blocksPerSm = 0;
+    B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, 0));
+    if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
+    if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
+    long long grid = (long long)ctx->smCount * blocksPerSm;
+    const long long needed = ((long long)p.numRays + BLOCK - 1) / BLOCK;
+    if (grid > needed) grid = needed;
+    if (grid < 1) grid = 1;
+    B2RT_CUDA(ctx, cudaMemsetAsync(p.warpCounter, 0, sizeof(int), stream));
+    kern<<<(unsigned)grid, BLOCK, 0, stream>>>(p);
+    B2RT_CHECK_LAUNCH(ctx, "traceWideKernel");
+    return B2RT_OK;
+}
+
+template <int BLOCK, int MIN_BLOCKS>
+static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
+{
+    const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
+    const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
+    if (flags & B2RT_TRACE_STATS)
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+}
+
+int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
+                    cudaStream_t stream)
+{
+    int rc = ensureWide(ctx);
+    if (rc) return rc;
+    WideParams p;
+    p.rays = static_cast<const float4*>(rays);
+    p.results = static_cast<int4*>(results);
+    p.nodes = ctx->wideNodes;
+    p.woop = ctx->wideWoop;
+    p.triIndex = ctx->wideTriIndex;
+    p.numRays = (int)numRays;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
+    p.warpCounter = ctx->warpCounter;
+    p.stats = ctx->statsDev;
+    if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 8 * sizeof(unsigned long long), stream));
+    switch (variant) {
+    default:
+    case 100: return launchWideFlags<256, 3>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM
+    case 101: return launchWideFlags<256, 2>(ctx, p, flags, stream);   // <= 128 regs, 16 warps/SM
+    case 102: return launchWideFlags<256, 4>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM
+    case 103: return launchWideFlags<128, 5>(ctx, p, flags, stream);   // <= 96 regs, 20 warps/SM
+    }
+}
+
+}  // namespace b2rt

@@ -205,6 +205,17 @@ int  b2rt_bvh_load(const char* path, b2rt_host_bvh** out);
 /* per-triangle normals as Scene does (rt/Scene.cc:72) */
 int  b2rt_tri_normals(const float* verts, const int32_t* tris, int num_tris, float* normals);
 
+/* Private 8-wide compressed form of a Compact2 BVH (csrc/wide_bvh.h): what b2rt_set_bvh builds for the wide
+ * traversal kernel (b2rt_trace_config.variant >= 100), exposed so it can be built and inspected without a GPU.
+ * 80-byte nodes, re-packed Woop rows (3 per triangle, +2 padding rows), one original triangle id per triangle.
+ * stats = { nodes, triangles, depth }. */
+typedef struct b2rt_wide_bvh b2rt_wide_bvh;
+int  b2rt_wide_build(const void* nodes, size_t node_bytes, const void* woop, size_t woop_bytes,
+                     const int32_t* tri_index, size_t tri_index_bytes, b2rt_wide_bvh** out);
+void b2rt_wide_free(b2rt_wide_bvh* w);
+int  b2rt_wide_arrays(const b2rt_wide_bvh* w, const void** nodes, size_t* node_bytes, const void** woop,
+                      size_t* woop_bytes, const int32_t** tri_index, size_t* tri_index_bytes, int stats[3]);
+
 /* Seeded procedural stand-ins for the README scenes (no network: bunny/conference/dragon/
  * hairball cannot be fetched).  kind: 0 blob (bunny-scale), 1 interior (conference-scale),
  * 2 knot (dragon-scale), 3 strands (hairball-scale).  SURVEY.md 8(d). */

@@ -136,3 +136,60 @@ def test_reference_launcher_abi(b2rt, oracle, ctx):
     lib.launch_countHitsKernel.restype = C.c_int32
     hits = lib.launch_countHitsKernel(C.c_int32(0), block, C.byref(inp))
     assert hits == int((got["id"] >= 0).sum())
+
+
+@pytest.mark.parametrize("variant", [100, 101, 102, 103])
+@pytest.mark.parametrize("kind,ntris", [("interior", 30000), ("strands", 30000), ("blob", 20000)])
+def test_wide_kernel_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
+    """The 8-wide compressed private form (csrc/trace_wide.cu): same acceptance rule as the binary kernel, and --
+    because both run the Woop test on the caller's rows -- bit-identical t, u, v wherever the ids agree."""
+    scene = b2rt.Scene.generate(kind, ntris, 20260101)
+    bvh = b2rt.BVH(scene)
+    rays = _primary_rays(b2rt, oracle, scene, 256, 192).copy()
+    rays["tmax"][5::97] = -1.0                                  # a few degenerate rays
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.writeBarycentrics = True
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    rb = b2rt.RayBuffer()
+    rb.setRays(rays)
+    ctx.set_trace_config(variant=1)
+    tracer.traceBatch(rb)
+    binary = rb.getResults().copy()
+    ctx.set_trace_config(variant=variant)
+    ms = tracer.traceBatch(rb)
+    got = rb.getResults().copy()
+    ctx.set_trace_config()
+    assert ms > 0.0
+    _check_closest(oracle, bvh.arrays(), rays, got)
+    same = got["id"] == binary["id"]
+    assert same.mean() >= ID_AGREE
+    hit = same & (got["id"] >= 0)
+    assert (got["t"][hit] == binary["t"][hit]).all() and (got["padA"][hit] == binary["padA"][hit]).all()
+    assert (got["id"][5::97] == -1).all() and (got["t"][5::97] == -1.0).all()
+
+
+def test_wide_kernel_any_hit_and_secondary(b2rt, oracle, ctx):
+    scene = b2rt.Scene.generate("interior", 30000, 3)
+    bvh = b2rt.BVH(scene)
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    origin, m = b2rt.camera_matrices(scene.camera, 256, 192)
+    rg = b2rt.RayGen(1 << 21, ctx)
+    prim = b2rt.RayBuffer()
+    rg.primary(prim, origin, m, 256, 192, scene.camera["far"])
+    ctx.set_trace_config(variant=100)
+    try:
+        tracer.traceBatch(prim)
+        sec = b2rt.RayBuffer()
+        rg.ao(sec, prim, scene, 4, 1.5, True)                   # any hit
+        tracer.traceBatch(sec)
+        rays, got = sec.getRays(), sec.getResults()
+        ref = oracle.trace_woop(bvh.arrays(), rays, any_hit=False)
+        assert ((got["id"] >= 0) == (ref["id"] >= 0)).mean() >= ID_AGREE
+        hit = got["id"] >= 0
+        assert (got["t"][hit] > 0).all() and (got["t"][hit] < 1.5).all()
+        sec.setNeedClosestHit(True)                             # the same rays as a diffuse (closest-hit) batch
+        tracer.traceBatch(sec)
+        _check_closest(oracle, bvh.arrays(), rays, sec.getResults(), ref)
+    finally:
+        ctx.set_trace_config()

@@ -49,7 +49,7 @@ def main():
             out[label] = counted / ms / 1e3
             print("%-16s %8.3f ms  %9.1f Mrays/s" % (label, ms, out[label]), flush=True)
         ref_res = res
-    sweeps = configs or ["v0", "v1", "v2", "v3", "v4", "v5"]
+    sweeps = configs or ["v1", "v6", "v7", "v100", "v101", "v102", "v103"]
     for s in sweeps:
         kw = {}
         for tok in s.split(","):
