@@ -278,6 +278,8 @@ def product_arm(args):
     wl = importlib.import_module(PKG + ".workloads")
     mg = importlib.import_module(PKG + ".multigpu")
     ctx = b2rt.Context.get(local_rank)
+    if args.variant >= 0 or args.top_nodes >= 0:
+        ctx.set_trace_config(variant=args.variant, top_nodes=args.top_nodes)
     name = args.workload
     cfg = wl.CONFIGS[name]
 
@@ -455,6 +457,8 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--impl", default="b2rt", choices=["b2rt", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--variant", type=int, default=-1, help="traversal kernel variant (b2rt_trace_config.variant); -1 = library default")
+    ap.add_argument("--top-nodes", type=int, default=-1)
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)

@@ -29,7 +29,7 @@ class TraceStats(C.Structure):
 
 
 class WorkCounters(C.Structure):
-    _fields_ = [(n, C.c_uint64) for n in ("rays", "nodes", "tris", "leaves", "ustage", "vstage", "hits", "max_stack")]
+    _fields_ = [(n, C.c_uint64) for n in ("rays", "nodes", "tris", "leaves", "ustage", "vstage", "hits", "max_stack", "max_chain")]
 
 
 class TraceConfig(C.Structure):

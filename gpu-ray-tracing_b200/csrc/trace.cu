@@ -33,12 +33,16 @@ struct TraceParams {
     int fetchThreshold;
     int* warpCounter;
     unsigned long long* stats;
+    cudaTextureObject_t nodesTex, woopTex;  // the same arrays behind the texture pipe (TEX variants)
 };
 
 constexpr int kLocalStack = 64;     // SplitBVHBuilder MaxDepth = 64 bounds the stack (SplitBVHBuilder.hh:43)
 constexpr unsigned kFull = 0xffffffffu;
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS>
+// TEX bit 0: node fetches outside the shared-memory top go through the texture pipe; bit 1: Woop rows do.
+// The L1 data is the same, but texture fetches use l1tex's TEX data pipe instead of the LSU data pipe that
+// ncu shows near saturation (l1tex__data_pipe_lsu_wavefronts 69-74 % of peak on the diffuse batch).
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
     extern __shared__ float4 s_dyn[];
@@ -146,6 +150,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     n0xy = lds128(a); n1xy = lds128(a + planeBytes); nz = lds128(a + 2u * planeBytes);
                     const int2 ch = lds64i(sTop + 3u * planeBytes + ((unsigned)nodeAddr << 1));
                     c0 = ch.x; c1 = ch.y;
+                } else if (TEX & 1) {
+                    n0xy = tex1Dfetch<float4>(p.nodesTex, nodeAddr); n1xy = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 1);
+                    nz = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 2);
+                    const float4 cn = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 3);
+                    c0 = __float_as_int(cn.x); c1 = __float_as_int(cn.y);
                 } else {
                     const float4* np = p.nodes + nodeAddr;
                     n0xy = ldg4(np); n1xy = ldg4(np + 1); nz = ldg4(np + 2);
@@ -187,9 +196,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             // postponed leaves
             while (leafAddr < 0) {
                 for (int triAddr = ~leafAddr;; triAddr += 3) {
-                    const float4 v00 = ldg4(p.woop + triAddr);
-                    const float4 v11 = ldg4(p.woop + triAddr + 1);
-                    const float4 v22 = ldg4(p.woop + triAddr + 2);
+                    float4 v00, v11, v22;
+                    if (TEX & 2) {
+                        v00 = tex1Dfetch<float4>(p.woopTex, triAddr); v11 = tex1Dfetch<float4>(p.woopTex, triAddr + 1);
+                        v22 = tex1Dfetch<float4>(p.woopTex, triAddr + 2);
+                    } else {
+                        v00 = ldg4(p.woop + triAddr); v11 = ldg4(p.woop + triAddr + 1); v22 = ldg4(p.woop + triAddr + 2);
+                    }
                     if (__float_as_int(v00.x) == (int)0x80000000) break;       // leaf terminator
                     if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
 
@@ -244,10 +257,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 // ---------------------------------------------------------------------------------------------
 struct Variant { int block; int stackSmem; int minBlocks; };
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
-    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS>;
+    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>;
     int topNodes = ctx->cfg.top_nodes < 0 ? (BLOCK >= 1024 ? 2048 : 512) : ctx->cfg.top_nodes;
     if (topNodes > ctx->topNodesAvail) topNodes = ctx->topNodesAvail;
     size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int);
@@ -272,20 +285,20 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS>
+template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX = 0>
 static int launchFlags(b2rt_ctx* ctx, TraceParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS) {
         // the instrumented build always writes barycentrics (one kernel fewer to carry)
-        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream)
-                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
     }
-    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream)
-                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream);
-    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream)
-                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
+    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
 }
 
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
@@ -302,6 +315,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
+    p.nodesTex = ctx->nodesTex; p.woopTex = ctx->woopTex;
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 8 * sizeof(unsigned long long), stream));
     int variant = ctx->cfg.variant;
     if (variant < 0) {
@@ -310,6 +324,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // 256-thread CTAs win on multi-million-ray batches
         variant = (numRays <= (4 << 20)) ? 6 : 1;
     }
+    if (variant >= 8 && variant <= 12 && (!ctx->nodesTex || !ctx->woopTex)) variant = (variant <= 10) ? 6 : 1;   // array too large for a 1D texture
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {
     default:
@@ -321,6 +336,11 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     case 5: return launchFlags<12, 256, 6>(ctx, p, flags, stream);   // <= 40 regs, 48 warps/SM
     case 6: return launchFlags<12, 1024, 1>(ctx, p, flags, stream);  // one CTA per SM: one big shared top-of-tree
     case 7: return launchFlags<12, 512, 2>(ctx, p, flags, stream);   // two CTAs per SM, <= 64 regs
+    case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // v6 with nodes through the texture pipe
+    case 9: return launchFlags<12, 1024, 1, 2>(ctx, p, flags, stream);  // v6 with Woop rows through the texture pipe
+    case 10: return launchFlags<12, 1024, 1, 3>(ctx, p, flags, stream); // v6 with both
+    case 11: return launchFlags<12, 256, 4, 1>(ctx, p, flags, stream);  // v1 with nodes through the texture pipe
+    case 12: return launchFlags<12, 256, 4, 2>(ctx, p, flags, stream);  // v1 with Woop rows through the texture pipe
     }
 }
 
@@ -414,6 +434,9 @@ __global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict_
     }
     for (int s = 16; s > 0; s >>= 1) { const unsigned long long t = __shfl_xor_sync(kFull, cS, s); cS = t > cS ? t : cS; }
     if ((threadIdx.x & 31) == 0) atomicMax(out + 7, cS);
+    unsigned long long cM = cN + cT;                // the longest dependent chain of one ray: node visits + triangle tests
+    for (int s = 16; s > 0; s >>= 1) { const unsigned long long t = __shfl_xor_sync(kFull, cM, s); cM = t > cM ? t : cM; }
+    if ((threadIdx.x & 31) == 0) atomicMax(out + 0, cM);
 }
 
 int countWork(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, cudaStream_t stream)
@@ -425,7 +448,7 @@ int countWork(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt
     unsigned long long h[8];
     B2RT_CUDA(ctx, cudaMemcpyAsync(h, ctx->statsDev, sizeof(h), cudaMemcpyDeviceToHost, stream));
     B2RT_CUDA(ctx, cudaStreamSynchronize(stream));
-    out->rays = (uint64_t)numRays; out->nodes = h[1]; out->tris = h[2]; out->leaves = h[3];
+    out->rays = (uint64_t)numRays; out->max_chain = h[0]; out->nodes = h[1]; out->tris = h[2]; out->leaves = h[3];
     out->ustage = h[4]; out->vstage = h[5]; out->hits = h[6]; out->max_stack = h[7];
     return B2RT_OK;
 }

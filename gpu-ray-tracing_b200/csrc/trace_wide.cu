@@ -29,23 +29,29 @@ struct WideParams {
     int fetchThreshold;
     int* warpCounter;
     unsigned long long* stats;
+    unsigned one;                           // 0x3F800000, passed as data so PRMT keeps its selector as the immediate
 };
 
 constexpr int kWideStack = 48;          // group entries; the collapsed tree is at most as deep as the binary one (<= 64, typ. < 12)
 constexpr unsigned kFullMask = 0xffffffffu;
 
 // byte j of `word` as the float 1 + byte * 2^-15 (exact): one PRMT, no integer-to-float conversion
+// `one` must hold 0x3F800000 in a register the compiler cannot see through: PRMT takes one immediate, and it
+// should be the SELECTOR (otherwise four selector constants get re-materialised before every PRMT).
 template <int J>
-__device__ __forceinline__ float byteToUnitFloat(unsigned word)
+__device__ __forceinline__ float byteToUnitFloat(unsigned word, unsigned one)
 {
-    return __uint_as_float(__byte_perm(word, 0x3F800000u, 0x7604u | (J << 4)));
+    unsigned r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(word), "r"(one), "n"(0x7604 | (J << 4)));
+    return __uint_as_float(r);
 }
 
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
     const int lane = threadIdx.x & 31;
     uint2 stack[kWideStack];
+    const unsigned one = p.one;                         // 0x3F800000 from the parameter block: opaque to ptxas (see byteToUnitFloat)
 
     float origx = 0, origy = 0, origz = 0, dirx = 0, diry = 0, dirz = 0;
     float idirx = 0, idiry = 0, idirz = 0, tmin = 0, hitT = 0, hitU = 0, hitV = 0;
@@ -139,12 +145,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                     const unsigned childBits4 = (meta4 >> 5) & 0x07070707u;
 #define B2RT_WIDE_CHILD(J)                                                                                          \
                     {                                                                                               \
-                        const float t0x = __fmaf_rn(byteToUnitFloat<J>(nearX), ax, bx);                           \
-                        const float t0y = __fmaf_rn(byteToUnitFloat<J>(nearY), ay, by);                           \
-                        const float t0z = __fmaf_rn(byteToUnitFloat<J>(nearZ), az, bz);                           \
-                        const float t1x = __fmaf_rn(byteToUnitFloat<J>(farX), ax, bx);                            \
-                        const float t1y = __fmaf_rn(byteToUnitFloat<J>(farY), ay, by);                            \
-                        const float t1z = __fmaf_rn(byteToUnitFloat<J>(farZ), az, bz);                            \
+                        const float t0x = __fmaf_rn(byteToUnitFloat<J>(nearX, one), ax, bx);                           \
+                        const float t0y = __fmaf_rn(byteToUnitFloat<J>(nearY, one), ay, by);                           \
+                        const float t0z = __fmaf_rn(byteToUnitFloat<J>(nearZ, one), az, bz);                           \
+                        const float t1x = __fmaf_rn(byteToUnitFloat<J>(farX, one) , ax, bx);                            \
+                        const float t1y = __fmaf_rn(byteToUnitFloat<J>(farY, one) , ay, by);                            \
+                        const float t1z = __fmaf_rn(byteToUnitFloat<J>(farZ, one) , az, bz);                            \
                         const float cmin = fmax3(t0x, t0y, fmaxf(t0z, tmin));                                      \
                         const float cmax = fmin3(t1x, t1y, fminf(t1z, hitT));                                      \
                         if (cmin <= cmax) hitmask |= ((childBits4 >> (8 * J)) & 0xFFu) << ((bitIndex4 >> (8 * J)) & 0xFFu); \
@@ -160,7 +166,15 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             }
 
             // ---- triangles of this node ---------------------------------------------------------
+            // Postponing (Ylitie et al. 2017, sec. 4.3): if fewer than 1/POSTPONE of the lanes that took this step
+            // hold triangles, intersecting now would run the Woop test at a few lanes wide (ncu: 3.6 active threads per
+            // triangle-loop instruction without it) -- park the group on the stack and keep traversing instead.
+            const int lanesHere = __popc(__activemask());
             while (T.y != 0u) {
+                if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < kWideStack - 2) {
+                    stack[sp++] = T;
+                    break;
+                }
                 if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
                 const int k = __ffs(T.y) - 1;
                 T.y &= T.y - 1u;
@@ -216,10 +230,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE>;
     int blocksPerSm = 0;
     B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, 0));
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
@@ -234,18 +248,18 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int BLOCK, int MIN_BLOCKS>
+template <int BLOCK, int MIN_BLOCKS, int POSTPONE>
 static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS)
-        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS>(ctx, p, stream)
-                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS>(ctx, p, stream);
-    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS>(ctx, p, stream)
-                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS>(ctx, p, stream);
-    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS>(ctx, p, stream)
-                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS>(ctx, p, stream);
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream);
 }
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
@@ -263,13 +277,16 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
+    p.one = 0x3F800000u;
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 8 * sizeof(unsigned long long), stream));
     switch (variant) {
     default:
-    case 100: return launchWideFlags<256, 3>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM
-    case 101: return launchWideFlags<256, 2>(ctx, p, flags, stream);   // <= 128 regs, 16 warps/SM
-    case 102: return launchWideFlags<256, 4>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM
-    case 103: return launchWideFlags<128, 5>(ctx, p, flags, stream);   // <= 96 regs, 20 warps/SM
+    case 100: return launchWideFlags<256, 3, 0>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM, no postponing
+    case 101: return launchWideFlags<256, 3, 5>(ctx, p, flags, stream);   // <= 80 regs, postpone below 1/5 of the lanes
+    case 102: return launchWideFlags<256, 4, 0>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM, no postponing
+    case 103: return launchWideFlags<256, 4, 5>(ctx, p, flags, stream);   // <= 64 regs, postpone below 1/5
+    case 104: return launchWideFlags<256, 4, 3>(ctx, p, flags, stream);   // postpone below 1/3
+    case 105: return launchWideFlags<256, 4, 2>(ctx, p, flags, stream);   // postpone below 1/2
     }
 }
 

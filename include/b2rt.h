@@ -121,6 +121,7 @@ int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out);
  * one-thread-per-ray kernel, not the production tracer.  Synchronous. */
 typedef struct {
     uint64_t rays, nodes, tris, leaves, ustage, vstage, hits, max_stack;
+    uint64_t max_chain;         /* largest (node visits + triangle tests) of a single ray: the serial tail of a launch */
 } b2rt_work_counters;
 int b2rt_count_work(b2rt_ctx* ctx, const void* rays_dev, int64_t num_rays, int any_hit,
                     b2rt_work_counters* out, void* stream);

@@ -31,11 +31,11 @@ def main():
     frame = wl.Frame(name, scene, bvh.arrays(), "cuda:0", ctx)
     counted = frame.counted_rays()
     print("batches", [(b.getSize(), c) for b, c in frame.batches], flush=True)
-    rb = frame.batches[0][0]
-    work = frame.tracer.countWork(rb)
-    n = work["rays"]
-    print("work/ray: nodes %.1f tris %.1f leaves %.1f hits %.3f maxstack %d" % (
-        work["nodes"] / n, work["tris"] / n, work["leaves"] / n, work["hits"] / n, work["max_stack"]))
+    for rb, _ in frame.batches[:2]:
+        work = frame.tracer.countWork(rb)
+        n = work["rays"]
+        print("work/ray: nodes %.1f tris %.1f leaves %.1f hits %.3f maxstack %d longest ray %d steps" % (
+            work["nodes"] / n, work["tris"] / n, work["leaves"] / n, work["hits"] / n, work["max_stack"], work["max_chain"]))
     out = {}
     # reference CUDA tracer
     if O.have_ref_gpu():
