@@ -178,6 +178,11 @@ void b2rt_destroy(b2rt_ctx* ctx)
     cudaFree(ctx->aabbDev); cudaFree(ctx->countDev);
     if (ctx->nodesTex) cudaDestroyTextureObject(ctx->nodesTex);
     if (ctx->woopTex) cudaDestroyTextureObject(ctx->woopTex);
+    if (ctx->sIn) {
+        cudaStreamDestroy(ctx->sIn); cudaStreamDestroy(ctx->sRun); cudaStreamDestroy(ctx->sOut);
+        for (int i = 0; i < b2rt_ctx::kHostChunks; i++) { cudaEventDestroy(ctx->evIn[i]); cudaEventDestroy(ctx->evK0[i]); cudaEventDestroy(ctx->evK1[i]); }
+        cudaEventDestroy(ctx->evT0); cudaEventDestroy(ctx->evT1);
+    }
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     delete ctx;
@@ -301,30 +306,58 @@ int b2rt_trace_host(b2rt_ctx* ctx, const void* raysHost, void* resultsHost, int6
     const size_t rayBytes = (size_t)numRays * sizeof(Ray), resBytes = (size_t)numRays * sizeof(RayResult);
     int rc = ensureStage(ctx, rayBytes + resBytes);
     if (rc) return rc;
+    // Three streams, up to kHostChunks chunks: the upload of chunk i+1, the trace of chunk i and the download of chunk
+    // i-1 overlap (PCIe is full duplex), so the call costs about max(upload, download) instead of their sum + the kernel.
+    if (!ctx->sIn) {
+        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sIn, cudaStreamNonBlocking));
+        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sRun, cudaStreamNonBlocking));
+        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sOut, cudaStreamNonBlocking));
+        for (int i = 0; i < b2rt_ctx::kHostChunks; i++) {
+            B2RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->evIn[i], cudaEventDisableTiming));
+            B2RT_CUDA(ctx, cudaEventCreate(&ctx->evK0[i]));
+            B2RT_CUDA(ctx, cudaEventCreate(&ctx->evK1[i]));
+        }
+        B2RT_CUDA(ctx, cudaEventCreate(&ctx->evT0));
+        B2RT_CUDA(ctx, cudaEventCreate(&ctx->evT1));
+    }
+    int chunks = (int)std::min<int64_t>(b2rt_ctx::kHostChunks, std::max<int64_t>(1, numRays / (256 * 1024)));
+    const int64_t per = ((numRays + chunks - 1) / chunks + 31) & ~int64_t(31);
+    chunks = (int)((numRays + per - 1) / per);
     char* dRays = static_cast<char*>(ctx->stage);
     char* dRes = dRays + rayBytes;
-    cudaEvent_t t0, t1;
-    B2RT_CUDA(ctx, cudaEventCreate(&t0));
-    B2RT_CUDA(ctx, cudaEventCreate(&t1));
-    cudaEventRecord(t0, 0);
-    cudaError_t e = cudaMemcpyAsync(dRays, raysHost, rayBytes, cudaMemcpyHostToDevice, 0);
-    // the kernel writes only id and t without WRITE_BARY (as CudaTracerKernels.hh:197): the pad
-    // words that travel back to the host are zero, not stale staging memory
-    if (e == cudaSuccess && !(flags & (B2RT_TRACE_WRITE_BARY | B2RT_TRACE_STATS)))
-        e = cudaMemsetAsync(dRes, 0, resBytes, 0);
-    if (e == cudaSuccess) e = cudaEventRecord(ctx->ev0, 0);
-    if (e == cudaSuccess) { rc = launchTrace(ctx, dRays, dRes, numRays, flags, 0); }
-    if (e == cudaSuccess && rc == 0) e = cudaEventRecord(ctx->ev1, 0);
-    if (e == cudaSuccess && rc == 0) e = cudaMemcpyAsync(resultsHost, dRes, resBytes, cudaMemcpyDeviceToHost, 0);
-    if (e == cudaSuccess && rc == 0) e = cudaEventRecord(t1, 0);
-    if (e == cudaSuccess && rc == 0) e = cudaEventSynchronize(t1);
-    if (e == cudaSuccess && rc == 0) {
-        if (msKernel) cudaEventElapsedTime(msKernel, ctx->ev0, ctx->ev1);
-        if (msTotal) cudaEventElapsedTime(msTotal, t0, t1);
+    const char* hRays = static_cast<const char*>(raysHost);
+    char* hRes = static_cast<char*>(resultsHost);
+    const bool clearPads = !(flags & (B2RT_TRACE_WRITE_BARY | B2RT_TRACE_STATS));
+    cudaError_t e = cudaEventRecord(ctx->evT0, ctx->sIn);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->sOut, ctx->evT0, 0);      // total time starts with the first upload
+    for (int c = 0; c < chunks && e == cudaSuccess && rc == 0; c++) {
+        const int64_t lo = c * per, n = std::min<int64_t>(per, numRays - lo);
+        e = cudaMemcpyAsync(dRays + lo * sizeof(Ray), hRays + lo * sizeof(Ray), (size_t)n * sizeof(Ray), cudaMemcpyHostToDevice, ctx->sIn);
+        if (e == cudaSuccess) e = cudaEventRecord(ctx->evIn[c], ctx->sIn);
+        // the kernel writes only id and t without WRITE_BARY (as CudaTracerKernels.hh:197): the pad words that
+        // travel back to the host are zero, not stale staging memory
+        if (e == cudaSuccess && clearPads) e = cudaMemsetAsync(dRes + lo * sizeof(RayResult), 0, (size_t)n * sizeof(RayResult), ctx->sRun);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->sRun, ctx->evIn[c], 0);
+        if (e == cudaSuccess) e = cudaEventRecord(ctx->evK0[c], ctx->sRun);
+        if (e == cudaSuccess) rc = launchTrace(ctx, dRays + lo * sizeof(Ray), dRes + lo * sizeof(RayResult), n, flags, ctx->sRun);
+        if (e == cudaSuccess && rc == 0) e = cudaEventRecord(ctx->evK1[c], ctx->sRun);
+        if (e == cudaSuccess && rc == 0) e = cudaStreamWaitEvent(ctx->sOut, ctx->evK1[c], 0);
+        if (e == cudaSuccess && rc == 0)
+            e = cudaMemcpyAsync(hRes + lo * sizeof(RayResult), dRes + lo * sizeof(RayResult), (size_t)n * sizeof(RayResult), cudaMemcpyDeviceToHost, ctx->sOut);
     }
-    cudaEventDestroy(t0); cudaEventDestroy(t1);
+    if (e == cudaSuccess && rc == 0) e = cudaEventRecord(ctx->evT1, ctx->sOut);
+    cudaError_t es = cudaStreamSynchronize(ctx->sOut);
+    cudaStreamSynchronize(ctx->sRun);
+    cudaStreamSynchronize(ctx->sIn);
+    if (e == cudaSuccess) e = es;
     if (rc) return rc;
     if (e != cudaSuccess) return setError(ctx, B2RT_ERR_CUDA, "b2rt_trace_host: %s", cudaGetErrorString(e));
+    if (msKernel) {
+        float sum = 0.0f;
+        for (int c = 0; c < chunks; c++) { float t = 0.0f; cudaEventElapsedTime(&t, ctx->evK0[c], ctx->evK1[c]); sum += t; }
+        *msKernel = sum;
+    }
+    if (msTotal) cudaEventElapsedTime(msTotal, ctx->evT0, ctx->evT1);
     return B2RT_OK;
 }
 

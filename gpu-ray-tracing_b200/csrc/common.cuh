@@ -51,6 +51,10 @@ struct b2rt_ctx {
     int* warpCounter = nullptr;                 // work counter for persistent warps
     unsigned long long* statsDev = nullptr;     // 8 counters for the instrumented kernel
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // b2rt_trace_host: upload / trace / download pipeline
+    static constexpr int kHostChunks = 8;
+    cudaStream_t sIn = nullptr, sRun = nullptr, sOut = nullptr;
+    cudaEvent_t evIn[kHostChunks] = {}, evK0[kHostChunks] = {}, evK1[kHostChunks] = {}, evT0 = nullptr, evT1 = nullptr;
 
     // scratch (grown on demand, never shrunk)
     void* scratch = nullptr;  size_t scratchBytes = 0;

@@ -102,18 +102,21 @@ class Frame:
             max_dist = far
         total = c.get("total_rays")
         if total:
-            # C5: ONE buffer of `total` diffuse rays (primaries x samples, truncated), this rank's slice
-            from .multigpu import shard_range
+            # C5: ONE buffer of `total` diffuse rays (primaries x samples).  Sharded over ranks in interleaved chunks of
+            # 1024 primaries (contiguous slices of an image-ordered buffer have unequal cost -- sky vs
+            # geometry -- so each rank takes every ws-th chunk); the last rank's slice is cut so the total is exact.
             n_prim_needed = (total + samples - 1) // samples
             big = RayGen(1 << 30, self.ctx)
-            lo_r, hi_r = shard_range(total, rank, ws)
-            p_lo, p_hi = lo_r // samples, min((hi_r + samples - 1) // samples, n_prim_needed)
-            sub = _slice_buffer(self.primary, p_lo, p_hi)
+            chunk = 1024
+            idx = torch.arange(n_prim_needed, device=self.device)
+            mine = idx[((idx // chunk) % ws) == rank]
+            sub = _gather_buffer(self.primary, mine)
             sec = RayBuffer(0, True, self.device)
             big.ao(sec, sub, scene, samples, max_dist, True)
             sec.setNeedClosestHit(True)
-            off = lo_r - p_lo * samples
-            sec = _slice_buffer(sec, off, off + (hi_r - lo_r), closest=True)
+            excess = n_prim_needed * samples - total
+            if excess and mine.numel() and int(mine[-1]) == n_prim_needed - 1:
+                sec = _slice_buffer(sec, 0, sec.getSize() - excess, closest=True)
             counted = int((sec.getRayBuffer_dev()[:, 7] >= 0).sum().item())
             self.batches.append((sec, counted))
             return
@@ -139,6 +142,20 @@ class Frame:
     def trace_all(self):
         """Trace every batch once; returns the summed kernel milliseconds (App.cc:194-204)."""
         return sum(self.tracer.traceBatch(rb) for rb, _ in self.batches)
+
+
+def _gather_buffer(rb, index):
+    """RayBuffer holding the rays and results of the given slots (identity id maps)."""
+    out = RayBuffer(0, rb.getNeedClosestHit(), rb.device)
+    n = int(index.numel())
+    out.resize(n)
+    if n:
+        out.m_rays[:n].copy_(rb.m_rays[index])
+        out.m_results[:n].copy_(rb.m_results[index])
+        ar = torch.arange(n, dtype=torch.int32, device=rb.device)
+        out.m_IDToSlot[:n].copy_(ar)
+        out.m_slotToID[:n].copy_(ar)
+    return out
 
 
 def _slice_buffer(rb, lo, hi, closest=None):
