@@ -155,7 +155,7 @@ int b2rt_create(int device, b2rt_ctx** out)
     ctx->ccMajor = prop.major; ctx->ccMinor = prop.minor;
     if ((e = cudaSetDevice(device)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->warpCounter, 64)) != cudaSuccess ||
-        (e = cudaMalloc(&ctx->statsDev, 8 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->statsDev, (16 + 3 * kTimelineWarps) * sizeof(unsigned long long))) != cudaSuccess ||
         (e = cudaMalloc(&ctx->aabbDev, 8 * sizeof(float))) != cudaSuccess ||
         (e = cudaMalloc(&ctx->countDev, sizeof(long long))) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
@@ -163,7 +163,7 @@ int b2rt_create(int device, b2rt_ctx** out)
         b2rt_destroy(ctx);
         return B2RT_ERR_CUDA;
     }
-    cudaMemset(ctx->statsDev, 0, 8 * sizeof(unsigned long long));
+    cudaMemset(ctx->statsDev, 0, (16 + 3 * kTimelineWarps) * sizeof(unsigned long long));
     *out = ctx;
     return B2RT_OK;
 }
@@ -229,11 +229,17 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     B2RT_CUDA(ctx, cudaMalloc(&ctx->nodes, nodeBytes));
     B2RT_CUDA(ctx, cudaMemcpy(ctx->nodes, out.data(), nodeBytes, cudaMemcpyHostToDevice));
     // Woop rows: the leaf loop fetches three rows before it looks at the terminator, so the copy
-    // carries two rows of padding past the last terminator (the reference relies on texture
-    // fetches returning zero out of range, kepler_dynamic_fetch.cu:328-334).
+    // carries padding rows past the last terminator (the reference relies on texture fetches
+    // returning zero out of range, kepler_dynamic_fetch.cu:328-334).  The first padding row is
+    // itself a terminator: row woopBytes/16 is a leaf without triangles, which the traversal
+    // kernel leaves in place of stack entries it hands to other lanes (trace.cu, SHARE).
     const cudaMemcpyKind kind = srcIsDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-    B2RT_CUDA(ctx, cudaMalloc(&ctx->woop, woopBytes + 32));
-    B2RT_CUDA(ctx, cudaMemset(reinterpret_cast<char*>(ctx->woop) + woopBytes, 0, 32));
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->woop, woopBytes + kWoopPadBytes));
+    B2RT_CUDA(ctx, cudaMemset(reinterpret_cast<char*>(ctx->woop) + woopBytes, 0, kWoopPadBytes));
+    {
+        const unsigned terminator = 0x80000000u;
+        B2RT_CUDA(ctx, cudaMemcpy(reinterpret_cast<char*>(ctx->woop) + woopBytes, &terminator, 4, cudaMemcpyHostToDevice));
+    }
     if (woopBytes) B2RT_CUDA(ctx, cudaMemcpy(ctx->woop, woop, woopBytes, kind));
     B2RT_CUDA(ctx, cudaMalloc(&ctx->triIndex, triIndexBytes + 16));
     if (triIndexBytes) B2RT_CUDA(ctx, cudaMemcpy(ctx->triIndex, triIndex, triIndexBytes, kind));
@@ -243,7 +249,7 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     for (int k = 0; k < 2; k++) {
         cudaTextureObject_t& t = k ? ctx->woopTex : ctx->nodesTex;
         if (t) { cudaDestroyTextureObject(t); t = 0; }
-        const size_t bytes = k ? woopBytes + 32 : nodeBytes;
+        const size_t bytes = k ? woopBytes + kWoopPadBytes : nodeBytes;
         if (bytes / 16 > (size_t(1) << 27) || bytes == 0) continue;
         cudaResourceDesc rd; memset(&rd, 0, sizeof(rd));
         rd.resType = cudaResourceTypeLinear;
@@ -375,12 +381,42 @@ int b2rt_count_work(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit
 int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out)
 {
     if (!ctx || !out) return B2RT_ERR_ARG;
-    unsigned long long h[8];
+    unsigned long long h[16];
     B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
     B2RT_CUDA(ctx, cudaDeviceSynchronize());
     B2RT_CUDA(ctx, cudaMemcpy(h, ctx->statsDev, sizeof(h), cudaMemcpyDeviceToHost));
     out->node_iters = h[0]; out->node_lanes = h[1]; out->tri_iters = h[2]; out->tri_lanes = h[3];
     out->fetches = h[4]; out->rays = h[5];
+    out->warps = h[12];
+    out->ns_pool_empty = out->ns_mean_exit = out->ns_last_exit = 0;
+    out->ns_exit_p50 = out->ns_exit_p90 = out->ns_exit_p99 = 0;
+    out->shares = h[13];
+    if (getenv("B2RT_DEBUG_TAIL")) fprintf(stderr, "tail: visits with busy lanes %llu, busy lanes %llu, lanes able to give %llu, stack entries of busy lanes %llu\n", h[14], h[15], h[6], h[7]);
+    if (h[12] && h[8] != ~0ull) {
+        const unsigned long long start40 = h[8] & 0xffffffffffull;
+        out->ns_last_exit = h[11] - h[8];
+        out->ns_pool_empty = (h[9] != ~0ull) ? h[9] - h[8] : 0;
+        out->ns_mean_exit = h[10] / h[12] - start40;        // valid unless the 40-bit timer wrapped during the launch (18 min period)
+        const size_t n = h[12] < (unsigned long long)kTimelineWarps ? (size_t)h[12] : (size_t)kTimelineWarps;
+        std::vector<unsigned long long> exits(n);
+        B2RT_CUDA(ctx, cudaMemcpy(exits.data(), ctx->statsDev + 16, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        if (getenv("B2RT_DEBUG_TAIL")) {
+            std::vector<unsigned long long> fetch(n), iters(n);
+            cudaMemcpy(fetch.data(), ctx->statsDev + 16 + kTimelineWarps, n * 8, cudaMemcpyDeviceToHost);
+            cudaMemcpy(iters.data(), ctx->statsDev + 16 + 2 * kTimelineWarps, n * 8, cudaMemcpyDeviceToHost);
+            std::vector<size_t> order(n);
+            for (size_t i = 0; i < n; i++) order[i] = i;
+            std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return exits[a] > exits[b]; });
+            for (size_t k = 0; k < 8 && k < n; k++) {
+                const size_t w = order[k * 5];
+                fprintf(stderr, "  warp %zu: exit %.1f us, last fetch %.1f us, since then %llu node iters, %llu tri iters\n", w,
+                        (exits[w] - h[8]) / 1e3, (fetch[w] - h[8]) / 1e3, iters[w] & 0xffffffffull, iters[w] >> 32);
+            }
+        }
+        std::sort(exits.begin(), exits.end());
+        auto pct = [&](double q) { const unsigned long long v = exits[(size_t)(q * (n - 1))]; return v > h[8] ? v - h[8] : 0ull; };
+        out->ns_exit_p50 = pct(0.50); out->ns_exit_p90 = pct(0.90); out->ns_exit_p99 = pct(0.99);
+    }
     return B2RT_OK;
 }
 

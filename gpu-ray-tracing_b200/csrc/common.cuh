@@ -22,6 +22,8 @@ struct MortonKey { int32_t oldSlot; uint32_t hash[6]; };       // ray/RayBufferK
 static_assert(sizeof(Ray) == 32 && sizeof(RayResult) == 16 && sizeof(MortonKey) == 28, "ABI");
 
 constexpr int kSentinel = B2RT_ENTRYPOINT_SENTINEL;
+constexpr int kTimelineWarps = 8192;    // per-warp exit times kept by the instrumented kernel (statsDev[16 ...])
+constexpr size_t kWoopPadBytes = 64;   // private Woop copy: one terminator row + three zero rows past the caller's rows
 
 }  // namespace b2rt
 
@@ -46,10 +48,10 @@ struct b2rt_ctx {
     int wideNumNodes = 0, wideNumTris = 0;
     bool hasWide = false;
 
-    b2rt_trace_config cfg = { -1, -1, -1, -1 };
+    b2rt_trace_config cfg = { -1, -1, -1, -1, -1 };
 
     int* warpCounter = nullptr;                 // work counter for persistent warps
-    unsigned long long* statsDev = nullptr;     // 8 counters for the instrumented kernel
+    unsigned long long* statsDev = nullptr;     // 16 counters for the instrumented kernel + kTimelineWarps exit times
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // b2rt_trace_host: upload / trace / download pipeline
     static constexpr int kHostChunks = 8;
@@ -117,6 +119,16 @@ __device__ __forceinline__ int2 lds64i(unsigned addr)
     int2 v;
     asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
     return v;
+}
+__device__ __forceinline__ void prefetchL1(const void* p)
+{
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
+}
+__device__ __forceinline__ unsigned long long globalTimerNs()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
 // sm_100a three-input float min/max (SASS FMNMX3)
 __device__ __forceinline__ float fmin3(float a, float b, float c)

@@ -156,10 +156,12 @@ bool buildWide8(const float* nodes2, size_t numNodes2, const float* woop, const 
             for (int s = 0; s < 8; s++)
                 cost[i][s] = ((s & 4) ? d[0] : -d[0]) + ((s & 2) ? d[1] : -d[1]) + ((s & 1) ? d[2] : -d[2]);
         }
+        // nodes with at most four children use slots 0..3 only: the kernel skips the upper half of such a node
+        const int numSlots = ch.size() <= 4 ? 4 : 8;
         for (size_t round = 0; round < ch.size(); round++) {
             int bi = -1, bs = -1; float bc = -3.0e38f;
             for (size_t i = 0; i < ch.size(); i++) if (!childDone[i])
-                for (int s = 0; s < 8; s++) if (!slotUsed[s] && cost[i][s] > bc) { bc = cost[i][s]; bi = (int)i; bs = s; }
+                for (int s = 0; s < numSlots; s++) if (!slotUsed[s] && cost[i][s] > bc) { bc = cost[i][s]; bi = (int)i; bs = s; }
             slotOf[bi] = bs; slotUsed[bs] = true; childDone[bi] = true;
         }
         int childAt[8]; for (int s = 0; s < 8; s++) childAt[s] = -1;

@@ -132,6 +132,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 unsigned hitmask = 0;
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
+                    // more than half of the nodes have <= 4 children, all in slots 0..3 (host/wide_bvh.cpp): skip the rest
+                    if (h == 1 && __float_as_uint(q1.w) == 0u) break;
                     const unsigned loX = __float_as_uint(h ? q2.y : q2.x), loY = __float_as_uint(h ? q2.w : q2.z);
                     const unsigned loZ = __float_as_uint(h ? q3.y : q3.x), hiX = __float_as_uint(h ? q3.w : q3.z);
                     const unsigned hiY = __float_as_uint(h ? q4.y : q4.x), hiZ = __float_as_uint(h ? q4.w : q4.z);
@@ -278,7 +280,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
-    if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 8 * sizeof(unsigned long long), stream));
+    if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
     switch (variant) {
     default:
     case 100: return launchWideFlags<256, 3, 0>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM, no postponing

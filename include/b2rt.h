@@ -67,6 +67,13 @@ typedef struct {
     uint64_t tri_lanes;
     uint64_t fetches;           /* warp-level ray fetches (atomics on the work counter) */
     uint64_t rays;
+    /* launch timeline from the global timer (binary kernel): nanoseconds after the first warp started */
+    uint64_t warps;             /* persistent warps that ran */
+    uint64_t ns_pool_empty;     /* first warp found the work counter past the last ray */
+    uint64_t ns_mean_exit;      /* mean warp exit time */
+    uint64_t ns_last_exit;      /* last warp exit = length of the launch; (last - mean) / last = idle tail */
+    uint64_t ns_exit_p50, ns_exit_p90, ns_exit_p99;    /* percentiles of the per-warp exit times */
+    uint64_t shares;            /* stack entries handed to idle lanes after the pool ran dry (subtree sharing) */
 } b2rt_trace_stats;
 
 /* Tunables of the traversal kernel; zero-initialise and override what you need. */
@@ -76,6 +83,7 @@ typedef struct {
                                    (kepler_dynamic_fetch.cu:48 uses 20); -1 = default */
     int blocks_per_sm;          /* persistent CTAs per SM; -1 = from occupancy */
     int variant;                /* kernel variant id; -1 = chosen from the batch size */
+    int node_break;             /* leave the inner-node loop when fewer lanes than this are still in it; <= 0 = default */
 } b2rt_trace_config;
 
 /* ---- context ---------------------------------------------------------------------------- */

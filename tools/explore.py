@@ -57,10 +57,22 @@ def main():
             if tok.startswith("t"): kw["top_nodes"] = int(tok[1:])
             if tok.startswith("f"): kw["fetch_threshold"] = int(tok[1:])
             if tok.startswith("b"): kw["blocks_per_sm"] = int(tok[1:])
+            if tok.startswith("n"): kw["node_break"] = int(tok[1:])
         ctx.set_trace_config(**kw)
         ms = median_ms(frame.trace_all)
         out[s] = counted / ms / 1e3
         print("%-16s %8.3f ms  %9.1f Mrays/s" % (s, ms, out[s]), flush=True)
+        if kw.get("variant", 0) < 100:
+            # SIMD efficiency and launch timeline, per batch (instrumented kernel, same configuration)
+            frame.tracer.collectStats = True
+            for rb, _ in frame.batches[:2]:
+                frame.tracer.traceBatch(rb)
+                st = frame.tracer.getStats()
+                print("    stats: TRV %.1f%% IST %.1f%% fetches %d shares %d | warps %d pool empty %.1f us, warp exit mean %.1f p50 %.1f p90 %.1f p99 %.1f last %.1f us" % (
+                    100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]), 100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"], st["shares"],
+                    st["warps"], st["ns_pool_empty"] / 1e3, st["ns_mean_exit"] / 1e3, st["ns_exit_p50"] / 1e3, st["ns_exit_p90"] / 1e3,
+                    st["ns_exit_p99"] / 1e3, st["ns_last_exit"] / 1e3))
+            frame.tracer.collectStats = False
     ctx.set_trace_config()
     frame.trace_all()
     if O.have_ref_gpu():
@@ -74,13 +86,6 @@ def main():
                 print("parity vs ref GPU: id agree %.6f, max rel t %.2e" % (same.mean(), rel.max(initial=0)))
             else:
                 print("parity vs ref GPU (any-hit): hit/miss agree %.6f" % ((mine["id"] >= 0) == (theirs["id"] >= 0)).mean())
-    # SIMD efficiency
-    frame.tracer.collectStats = True
-    frame.trace_all()
-    st = frame.tracer.getStats()
-    frame.tracer.collectStats = False
-    print("SIMD eff (last batch): TRV %.1f%%  IST %.1f%%  fetches %d" % (
-        100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]), 100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"]))
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", "explore_%s.json" % name), "w") as f:
         json.dump(out, f, indent=1)
