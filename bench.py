@@ -278,8 +278,8 @@ def product_arm(args):
     wl = importlib.import_module(PKG + ".workloads")
     mg = importlib.import_module(PKG + ".multigpu")
     ctx = b2rt.Context.get(local_rank)
-    if args.variant >= 0 or args.top_nodes >= 0:
-        ctx.set_trace_config(variant=args.variant, top_nodes=args.top_nodes)
+    if args.variant >= 0 or args.top_nodes >= 0 or args.l2_prefetch >= 0:
+        ctx.set_trace_config(variant=args.variant, top_nodes=args.top_nodes, l2_prefetch=args.l2_prefetch)
     name = args.workload
     cfg = wl.CONFIGS[name]
 
@@ -459,6 +459,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--variant", type=int, default=-1, help="traversal kernel variant (b2rt_trace_config.variant); -1 = library default")
     ap.add_argument("--top-nodes", type=int, default=-1)
+    ap.add_argument("--l2-prefetch", type=int, default=-1, help="b2rt_trace_config.l2_prefetch (0 off, 1 on, -1 library default)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)

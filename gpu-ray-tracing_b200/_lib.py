@@ -26,7 +26,7 @@ class B2rtError(RuntimeError):
 
 class TraceStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("node_iters", "node_lanes", "tri_iters", "tri_lanes", "fetches", "rays", "warps", "ns_pool_empty",
-                                           "ns_mean_exit", "ns_last_exit", "ns_exit_p50", "ns_exit_p90", "ns_exit_p99", "shares")]
+                                           "ns_mean_exit", "ns_last_exit", "ns_exit_p50", "ns_exit_p90", "ns_exit_p99", "ns_straggler_fetch", "straggler_node_iters", "straggler_tri_iters")]
 
 
 class WorkCounters(C.Structure):
@@ -34,7 +34,7 @@ class WorkCounters(C.Structure):
 
 
 class TraceConfig(C.Structure):
-    _fields_ = [("top_nodes", C.c_int), ("fetch_threshold", C.c_int), ("blocks_per_sm", C.c_int), ("variant", C.c_int), ("node_break", C.c_int)]
+    _fields_ = [("top_nodes", C.c_int), ("fetch_threshold", C.c_int), ("blocks_per_sm", C.c_int), ("variant", C.c_int), ("node_break", C.c_int), ("l2_prefetch", C.c_int)]
 
 
 class BuildParams(C.Structure):

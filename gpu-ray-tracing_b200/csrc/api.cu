@@ -152,6 +152,7 @@ int b2rt_create(int device, b2rt_ctx** out)
     b2rt_ctx* ctx = new b2rt_ctx();
     ctx->device = device;
     ctx->smCount = prop.multiProcessorCount;
+    ctx->l2Bytes = (size_t)prop.l2CacheSize;
     ctx->ccMajor = prop.major; ctx->ccMinor = prop.minor;
     if ((e = cudaSetDevice(device)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->warpCounter, 64)) != cudaSuccess ||
@@ -231,8 +232,7 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     // Woop rows: the leaf loop fetches three rows before it looks at the terminator, so the copy
     // carries padding rows past the last terminator (the reference relies on texture fetches
     // returning zero out of range, kepler_dynamic_fetch.cu:328-334).  The first padding row is
-    // itself a terminator: row woopBytes/16 is a leaf without triangles, which the traversal
-    // kernel leaves in place of stack entries it hands to other lanes (trace.cu, SHARE).
+    // itself a terminator, so a leaf loop that runs off a malformed last leaf stops there.
     const cudaMemcpyKind kind = srcIsDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     B2RT_CUDA(ctx, cudaMalloc(&ctx->woop, woopBytes + kWoopPadBytes));
     B2RT_CUDA(ctx, cudaMemset(reinterpret_cast<char*>(ctx->woop) + woopBytes, 0, kWoopPadBytes));
@@ -390,8 +390,7 @@ int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out)
     out->warps = h[12];
     out->ns_pool_empty = out->ns_mean_exit = out->ns_last_exit = 0;
     out->ns_exit_p50 = out->ns_exit_p90 = out->ns_exit_p99 = 0;
-    out->shares = h[13];
-    if (getenv("B2RT_DEBUG_TAIL")) fprintf(stderr, "tail: visits with busy lanes %llu, busy lanes %llu, lanes able to give %llu, stack entries of busy lanes %llu\n", h[14], h[15], h[6], h[7]);
+    out->ns_straggler_fetch = out->straggler_node_iters = out->straggler_tri_iters = 0;
     if (h[12] && h[8] != ~0ull) {
         const unsigned long long start40 = h[8] & 0xffffffffffull;
         out->ns_last_exit = h[11] - h[8];
@@ -400,18 +399,14 @@ int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out)
         const size_t n = h[12] < (unsigned long long)kTimelineWarps ? (size_t)h[12] : (size_t)kTimelineWarps;
         std::vector<unsigned long long> exits(n);
         B2RT_CUDA(ctx, cudaMemcpy(exits.data(), ctx->statsDev + 16, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-        if (getenv("B2RT_DEBUG_TAIL")) {
-            std::vector<unsigned long long> fetch(n), iters(n);
-            cudaMemcpy(fetch.data(), ctx->statsDev + 16 + kTimelineWarps, n * 8, cudaMemcpyDeviceToHost);
-            cudaMemcpy(iters.data(), ctx->statsDev + 16 + 2 * kTimelineWarps, n * 8, cudaMemcpyDeviceToHost);
-            std::vector<size_t> order(n);
-            for (size_t i = 0; i < n; i++) order[i] = i;
-            std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return exits[a] > exits[b]; });
-            for (size_t k = 0; k < 8 && k < n; k++) {
-                const size_t w = order[k * 5];
-                fprintf(stderr, "  warp %zu: exit %.1f us, last fetch %.1f us, since then %llu node iters, %llu tri iters\n", w,
-                        (exits[w] - h[8]) / 1e3, (fetch[w] - h[8]) / 1e3, iters[w] & 0xffffffffull, iters[w] >> 32);
-            }
+        {
+            const size_t last = std::max_element(exits.begin(), exits.end()) - exits.begin();
+            unsigned long long fetch = 0, iters = 0;
+            B2RT_CUDA(ctx, cudaMemcpy(&fetch, ctx->statsDev + 16 + kTimelineWarps + last, 8, cudaMemcpyDeviceToHost));
+            B2RT_CUDA(ctx, cudaMemcpy(&iters, ctx->statsDev + 16 + 2 * kTimelineWarps + last, 8, cudaMemcpyDeviceToHost));
+            out->ns_straggler_fetch = fetch > h[8] ? fetch - h[8] : 0;
+            out->straggler_node_iters = iters & 0xffffffffull;
+            out->straggler_tri_iters = iters >> 32;
         }
         std::sort(exits.begin(), exits.end());
         auto pct = [&](double q) { const unsigned long long v = exits[(size_t)(q * (n - 1))]; return v > h[8] ? v - h[8] : 0ull; };

@@ -32,6 +32,7 @@ constexpr size_t kWoopPadBytes = 64;   // private Woop copy: one terminator row 
 struct b2rt_ctx {
     int device = 0;
     int smCount = 0, ccMajor = 0, ccMinor = 0;
+    size_t l2Bytes = 0;
     std::string lastError;
     int64_t launches = 0;
 
@@ -48,7 +49,7 @@ struct b2rt_ctx {
     int wideNumNodes = 0, wideNumTris = 0;
     bool hasWide = false;
 
-    b2rt_trace_config cfg = { -1, -1, -1, -1, -1 };
+    b2rt_trace_config cfg = { -1, -1, -1, -1, -1, -1 };
 
     int* warpCounter = nullptr;                 // work counter for persistent warps
     unsigned long long* statsDev = nullptr;     // 16 counters for the instrumented kernel + kTimelineWarps exit times
@@ -120,9 +121,9 @@ __device__ __forceinline__ int2 lds64i(unsigned addr)
     asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
     return v;
 }
-__device__ __forceinline__ void prefetchL1(const void* p)
+__device__ __forceinline__ void prefetchL2(const void* p)
 {
-    asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
 }
 __device__ __forceinline__ unsigned long long globalTimerNs()
 {

@@ -32,35 +32,19 @@ struct TraceParams {
     int topF4;              // float4 elements of the node array staged in shared memory
     int fetchThreshold;
     int nodeBreak;          // leave the node loop when fewer lanes than this are in it (0 = never)
+    int pfNodeLines, pfWoopLines;   // 128-byte lines of the node / Woop arrays to pull into L2 when the launch starts (0 = none)
     int* warpCounter;
     unsigned long long* stats;
     cudaTextureObject_t nodesTex, woopTex;  // the same arrays behind the texture pipe (TEX variants)
-    int dummyLeaf;          // ~row of a lone terminator row in the private Woop copy: a leaf without triangles
 };
 
 constexpr int kLocalStack = 64;     // SplitBVHBuilder MaxDepth = 64 bounds the stack (SplitBVHBuilder.hh:43)
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kShareSteps = 4;      // SHARE, tail of the launch: node steps between two visits of the queue
 
 // TEX bit 0: node fetches outside the shared-memory top go through the texture pipe; bit 1: Woop rows do.
 // The L1 data is the same, but texture fetches use l1tex's TEX data pipe instead of the LSU data pipe that
 // ncu shows near saturation (l1tex__data_pipe_lsu_wavefronts 69-74 % of peak on the diffuse batch).
-// SHARE: subtree sharing in the tail of a launch.  Once the work counter has run dry the launch is a set of dependent
-// chains: every remaining ray needs its remaining node visits one after the other (~300 ns each), while most lanes
-// and warps of the SM have nothing left to do (measured on C2: pool empty at 91 us, 90 % of the warps gone at 114 us,
-// last warp at 180 us).  With SHARE, lanes that are still traversing hand the LOWEST entries of their stacks -- whole
-// subtrees -- to a queue in shared memory; idle lanes of any warp of the CTA take them, re-read the ray, traverse the
-// subtree with the hit distance known at hand-over and merge their hit into the ray's result record with a 64-bit
-// atomicMin on (t, Woop row).  After the CTA's last warp has left the loop the CTA rewrites the records of its shared
-// rays into the final form (triangle id, barycentrics).  Nothing waits on anything but the queue's try-lock.
-struct ShareArea {
-    int lock;               // 0 free, 1 taken (try-lock; idle warps retry, busy warps just skip the visit)
-    int head, tail;         // queue positions, free-running; changed under the lock
-    int idleWarps;          // warps of the CTA without a ray in flight (includes warps that have left)
-    int listCount;          // shared rays of this CTA (entries of list[])
-    int pad[3];
-};
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX, bool SHARE>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
     extern __shared__ float4 s_dyn[];
@@ -73,6 +57,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
     int* s_stack = reinterpret_cast<int*>(s_dyn) + threadIdx.x;              // slot k at s_stack[k * BLOCK]
     const int topF4 = p.topF4;
     const int topNodes = topF4 >> 2;
+    // A launch that finds the BVH in DRAM pays a full miss on every step of every ray's dependent chain until the
+    // arrays have drifted into L2 by themselves.  Ask for them up front instead: one prefetch per 128-byte line,
+    // spread over the grid, streams at DRAM bandwidth (tens of MB: a few microseconds) behind the first rays.
+    {
+        const size_t stride = (size_t)gridDim.x * BLOCK;
+        for (size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x; i < (size_t)p.pfNodeLines; i += stride) prefetchL2(p.nodes + i * 8);
+        for (size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x; i < (size_t)p.pfWoopLines; i += stride) prefetchL2(p.woop + i * 8);
+    }
     float4* s_plane = s_dyn + (STACK_SMEM * BLOCK) / 4;
     {
         int2* s_child = reinterpret_cast<int2*>(s_plane + 3 * topNodes);
@@ -83,12 +75,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             else s_child[node] = make_int2(__float_as_int(v.x), __float_as_int(v.y));
         }
     }
-    // SHARE: [ShareArea][queue: BLOCK int4 (ray, stack entry, hit distance)][list: 2 * BLOCK ray indices]
-    constexpr int kQueue = BLOCK, kListCap = 2 * BLOCK, kWarps = BLOCK / 32;
-    ShareArea* s_share = reinterpret_cast<ShareArea*>(reinterpret_cast<char*>(s_plane) + (size_t)topNodes * 56);
-    int4* s_queue = reinterpret_cast<int4*>(s_share + 1);
-    int* s_list = reinterpret_cast<int*>(s_queue + kQueue);
-    if (SHARE && threadIdx.x == 0) { s_share->lock = 0; s_share->head = 0; s_share->tail = 0; s_share->idleWarps = 0; s_share->listCount = 0; }
     __syncthreads();
     unsigned sTop = (unsigned)__cvta_generic_to_shared(s_plane);              // 32-bit shared address of plane 0
     asm volatile("mov.u32 %0, %0;" : "+r"(sTop));      // opaque: keep it in a register instead of re-deriving it per node
@@ -107,14 +93,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
     int tos = kSentinel;                // top of stack, in a register
     int sp = 0;                         // number of entries held in memory
     bool poolEmpty = false;             // warp-uniform: the work counter ran past numRays
-    float probe = 0.f;                  // TEX & 12 cost probes only
-    // subtree sharing (SHARE)
-    bool viaAtomic = false;             // this lane's ray is shared (or the lane works on a handed-over subtree): merge by atomicMin
-    int giveSlot = 2;                   // lowest stack slot not yet handed over (slots 0 and 1 hold the sentinel)
-    bool countedIdle = false;           // warp-uniform: this warp is counted in ShareArea::idleWarps
 
     unsigned long long stNodeIters = 0, stNodeLanes = 0, stTriIters = 0, stTriLanes = 0, stFetches = 0;
-    unsigned long long stStart = 0, stPoolEmpty = 0, stShares = 0, stLastFetch = 0, stItersAtFetch = 0;
+    unsigned long long stStart = 0, stPoolEmpty = 0, stLastFetch = 0, stItersAtFetch = 0;
     if (STATS) stStart = globalTimerNs();
 
     auto warpSum = [&](unsigned long long v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o); return v; };
@@ -132,21 +113,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
         // ---- store finished rays, refill -------------------------------------------------
         const bool terminated = (nodeAddr == kSentinel);
         if (terminated && rayidx >= 0) {
-            if (SHARE && viaAtomic) {
-                // shared ray: (t, Woop row) competes with what the other lanes working on this ray found
-                if (hitIndex != -1)
-                    atomicMin(reinterpret_cast<unsigned long long*>(p.results + rayidx),
-                              ((unsigned long long)__float_as_uint(hitT) << 32) | (unsigned)hitIndex);
-            } else {
-                const int id = (hitIndex == -1) ? -1 : __ldg(p.triIndex + hitIndex);
-                if ((TEX & 12) && probe == 123.456f) hitT = probe;      // keeps the probes alive, never true in practice
-                if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
-                else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
-            }
+            const int id = (hitIndex == -1) ? -1 : __ldg(p.triIndex + hitIndex);
+            if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
+            else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
             rayidx = -1;
         }
-        // a warp of this CTA without work means the pool is empty: start visiting the queue
-        if (SHARE && !poolEmpty && *reinterpret_cast<volatile int*>(&s_share->idleWarps) > 0) poolEmpty = true;
         const unsigned maskT = __ballot_sync(kFull, terminated);
         if (maskT != 0 && !poolEmpty) {
             const int numT = __popc(maskT);
@@ -175,122 +146,17 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     stackStore(0, kSentinel);
                     sp = 1; tos = kSentinel;
                     leafAddr = 0; nodeAddr = 0; hitIndex = -1;
-                    if (SHARE) { giveSlot = 2; viaAtomic = false; }
                 }
             }
         }
-        if (SHARE && poolEmpty) {
-            bool leave = false;
-            for (;;) {
-                const bool busy = (nodeAddr != kSentinel);
-                const unsigned busyMask = __ballot_sync(kFull, busy);
-                const unsigned idleMask = ~busyMask;
-                // hand over only from rays whose t is a positive float (its bits then order like the value)
-                if (giveSlot > sp) giveSlot = max(sp, 2);           // the stack has shrunk below entries handed over earlier
-                const bool canGive = busy && sp > giveSlot && tmin >= 0.0f;
-                const unsigned giveMask = __ballot_sync(kFull, canGive);
-                volatile ShareArea* sh = s_share;
-                if (STATS && busyMask != 0) {
-                    int depth = busy ? sp - 1 : 0;
-                    for (int o = 16; o > 0; o >>= 1) depth += __shfl_xor_sync(kFull, depth, o);
-                    if (lane == 0) {
-                        atomicAdd(p.stats + 14, 1ull); atomicAdd(p.stats + 15, (unsigned long long)__popc(busyMask));
-                        atomicAdd(p.stats + 6, (unsigned long long)__popc(giveMask)); atomicAdd(p.stats + 7, (unsigned long long)depth);
-                    }
-                }
-                const int qLen = sh->tail - sh->head;               // a hint; the exact values are read under the lock
-                const bool wantPop = idleMask != 0 && qLen > 0;
-                const bool wantPush = giveMask != 0 && qLen < kQueue / 2 && (idleMask != 0 || sh->idleWarps > 0);
-                if (wantPop || wantPush) {
-                    int got = 0;
-                    if (lane == 0) got = (atomicCAS(&s_share->lock, 0, 1) == 0);
-                    got = __shfl_sync(kFull, got, 0);
-                    if (got) {
-                        __threadfence_block();
-                        int h = sh->head, t = sh->tail, listCount = sh->listCount;
-                        const unsigned below = (1u << lane) - 1u;
-                        bool fresh = false;
-                        if (wantPush) {
-                            // lanes whose ray is not shared yet also need a slot in the CTA's list of shared rays
-                            const bool needList = canGive && !viaAtomic;
-                            const unsigned needMask = __ballot_sync(kFull, needList);
-                            const bool listOk = !needList || listCount + __popc(needMask & below) < kListCap;
-                            const unsigned okMask = __ballot_sync(kFull, canGive && listOk);
-                            const int space = kQueue - (t - h);
-                            const int rank = __popc(okMask & below);
-                            if (canGive && listOk && rank < space) {
-                                if (!viaAtomic) {
-                                    s_list[listCount + __popc(needMask & below)] = rayidx;
-                                    *reinterpret_cast<unsigned long long*>(p.results + rayidx) = ~0ull;     // "nothing found yet"
-                                    viaAtomic = true; fresh = true;
-                                }
-                                const int entry = stackLoad(giveSlot);
-                                stackStore(giveSlot, p.dummyLeaf);
-                                giveSlot++;
-                                s_queue[(unsigned)(t + rank) % kQueue] = make_int4(rayidx, entry, __float_as_int(hitT), 0);
-                                if (STATS) stShares++;
-                            }
-                            // (the lanes that give are the first ones in lane order, so the new list slots are contiguous)
-                            const unsigned gaveFresh = __ballot_sync(kFull, fresh);
-                            listCount += __popc(gaveFresh);
-                            t += min(__popc(okMask), max(space, 0));
-                            if (gaveFresh) __threadfence();         // the cleared records are in L2 before anybody can take the entries
-                            __syncwarp();
-                        }
-                        const int nPop = min(__popc(idleMask), t - h);
-                        const int prank = __popc(idleMask & below);
-                        int4 item = make_int4(-1, 0, 0, 0);
-                        if (!busy && prank < nPop) item = s_queue[(unsigned)(h + prank) % kQueue];
-                        __syncwarp();
-                        if (lane == 0) {
-                            sh->head = h + nPop; sh->tail = t; sh->listCount = listCount;
-                            if (nPop > 0 && countedIdle) atomicSub(&s_share->idleWarps, 1);
-                            __threadfence_block();
-                            atomicExch(&s_share->lock, 0);
-                        }
-                        if (nPop > 0) countedIdle = false;
-                        if (item.x >= 0) {
-                            // a handed-over subtree: the ray again, the hit distance of the moment it was handed over
-                            rayidx = item.x;
-                            const float4 o = ldg4(p.rays + 2 * (size_t)rayidx);
-                            const float4 d = ldg4(p.rays + 2 * (size_t)rayidx + 1);
-                            origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
-                            dirx = d.x; diry = d.y; dirz = d.z; hitT = __int_as_float(item.z);
-                            const float ooeps = 8.271806125530277e-25f;
-                            idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-                            idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-                            idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-                            oodx = origx * idirx; oody = origy * idiry; oodz = origz * idirz;
-                            hitIndex = -1; viaAtomic = true; giveSlot = 2;
-                            stackStore(0, kSentinel);
-                            sp = 1; tos = kSentinel;
-                            // an inner node starts the node loop; a leaf goes straight to the postponed slot, with the empty
-                            // leaf behind it so that the loops below run their usual course
-                            if (item.y >= 0) { nodeAddr = item.y; leafAddr = 0; } else { leafAddr = item.y; nodeAddr = p.dummyLeaf; }
-                        }
-                    }
-                }
-                if (__ballot_sync(kFull, nodeAddr != kSentinel) != 0) break;        // somebody has work: traverse
-                // the whole warp is idle: say so, then wait for entries or for everybody else to run dry as well
-                if (!countedIdle) {
-                    if (lane == 0) atomicAdd(&s_share->idleWarps, 1);
-                    countedIdle = true;
-                }
-                if (sh->tail - sh->head <= 0 && sh->idleWarps >= kWarps) { leave = true; break; }
-                __nanosleep(200);
-            }
-            if (leave) break;
-        }
-        if (!SHARE || !poolEmpty) { if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break; }     // warp out of work
+        if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break;     // warp out of work
 
-        // after the pool is empty: without SHARE never leave the loop early; with SHARE come back up whenever a lane is free
         const int nodeBreak = poolEmpty ? 0 : p.nodeBreak;
-        const int threshold = poolEmpty ? (SHARE ? 33 : 0) : p.fetchThreshold;
+        const int threshold = poolEmpty ? 0 : p.fetchThreshold;
 
         // ---- traversal --------------------------------------------------------------------
         while (nodeAddr != kSentinel) {
             // inner nodes, until every participating lane holds a postponed leaf
-            int tailSteps = kShareSteps;        // SHARE, pool empty: go back up for sharing every few node steps
             while ((unsigned)nodeAddr < (unsigned)kSentinel) {
                 if (STATS) { const unsigned am = __activemask(); stNodeLanes++; if (lane == __ffs(am) - 1) stNodeIters++; }
                 float4 n0xy, n1xy, nz;
@@ -310,18 +176,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     n0xy = ldg4(np); n1xy = ldg4(np + 1); nz = ldg4(np + 2);
                     const int2 ch = __ldg(reinterpret_cast<const int2*>(np + 3));
                     c0 = ch.x; c1 = ch.y;
-                    if (TEX & 4) {          // probe: how much does one more 16-byte load per node cost?
-                        const float4 extra = ldg4(np + 4);
-                        probe += extra.x;
-                    }
-                }
-                if (TEX & 8) {              // probe: how much do twelve more ALU instructions per node cost?
-                    unsigned w = __float_as_uint(n0xy.x);
-#pragma unroll
-                    for (int k = 0; k < 6; k++) {
-                        w = __byte_perm(w, __float_as_uint(nz.x), 0x4123 + k);
-                        probe = __fmaf_rn(__uint_as_float(w), idirx, probe);
-                    }
                 }
 
                 const float c0lox = __fmaf_rn(n0xy.x, idirx, -oodx), c0hix = __fmaf_rn(n0xy.y, idirx, -oodx);
@@ -357,7 +211,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     if (!__any_sync(am, leafAddr >= 0)) break;
                     if (__popc(am) < nodeBreak) break;
                 }
-                if (SHARE && poolEmpty && --tailSteps == 0) break;
             }
 
             // postponed leaves
@@ -399,39 +252,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 
             // dynamic fetch: too few lanes left -> leave and refill the idle ones
             if (__popc(__activemask()) < threshold) break;
-            if (SHARE && !poolEmpty && *reinterpret_cast<volatile int*>(&s_share->idleWarps) > 0) break;
-        }
-    }
-
-    if (SHARE) {
-        // Every lane that worked on a shared ray of this CTA belongs to this CTA and has merged its hit.  Turn the merged
-        // (Woop row, t) records into the final form: triangle id through triIndex, barycentrics recomputed with the
-        // arithmetic of the leaf loop (same operands, same order: the same bits), t = tmax for a miss.
-        __syncthreads();
-        const int shared = s_share->listCount;
-        for (int i = threadIdx.x; i < shared; i += BLOCK) {
-            const int r = s_list[i];
-            const unsigned long long key = __ldcg(reinterpret_cast<const unsigned long long*>(p.results + r));
-            const int row = (int)(unsigned)(key & 0xffffffffull);
-            const float4 d = ldg4(p.rays + 2 * (size_t)r + 1);
-            int id = -1;
-            float t = d.w, u = 0.f, v = 0.f;
-            if (row != -1) {
-                id = __ldg(p.triIndex + row);
-                t = __uint_as_float((unsigned)(key >> 32));
-                if (BARY) {
-                    const float4 o = ldg4(p.rays + 2 * (size_t)r);
-                    const float4 v11 = ldg4(p.woop + row + 1), v22 = ldg4(p.woop + row + 2);
-                    const float Ox = __fmaf_rn(o.z, v11.z, __fmaf_rn(o.y, v11.y, __fmaf_rn(o.x, v11.x, v11.w)));
-                    const float Dx = __fmaf_rn(d.z, v11.z, __fmaf_rn(d.y, v11.y, __fmul_rn(d.x, v11.x)));
-                    u = __fmaf_rn(t, Dx, Ox);
-                    const float Oy = __fmaf_rn(o.z, v22.z, __fmaf_rn(o.y, v22.y, __fmaf_rn(o.x, v22.x, v22.w)));
-                    const float Dy = __fmaf_rn(d.z, v22.z, __fmaf_rn(d.y, v22.y, __fmul_rn(d.x, v22.x)));
-                    v = __fmaf_rn(t, Dy, Oy);
-                }
-            }
-            if (BARY) p.results[r] = make_int4(id, __float_as_int(t), __float_as_int(u), __float_as_int(v));
-            else reinterpret_cast<int2*>(p.results)[r * 2] = make_int2(id, __float_as_int(t));
         }
     }
 
@@ -444,7 +264,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             stTriIters += __shfl_xor_sync(kFull, stTriIters, o);
             stTriLanes += __shfl_xor_sync(kFull, stTriLanes, o);
             stFetches += __shfl_xor_sync(kFull, stFetches, o);
-            stShares += __shfl_xor_sync(kFull, stShares, o);
         }
         if (lane == 0) {
             atomicAdd(p.stats + 0, stNodeIters); atomicAdd(p.stats + 1, stNodeLanes);
@@ -457,7 +276,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             atomicAdd(p.stats + 10, now & 0xffffffffffull);     // low 40 bits: sums of <= 2^20 warps cannot overflow
             atomicMax(p.stats + 11, now);
             atomicAdd(p.stats + 12, 1ull);
-            atomicAdd(p.stats + 13, stShares);
             const int gw = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
             if (gw < kTimelineWarps) p.stats[16 + gw] = now;
             if (gw < kTimelineWarps) { p.stats[16 + kTimelineWarps + gw] = stLastFetch; p.stats[16 + 2 * kTimelineWarps + gw] = dbgIters - stItersAtFetch; }
@@ -470,14 +288,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 // ---------------------------------------------------------------------------------------------
 struct Variant { int block; int stackSmem; int minBlocks; };
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX, bool SHARE>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
-    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX, SHARE>;
+    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>;
     int topNodes = ctx->cfg.top_nodes < 0 ? (BLOCK >= 1024 ? 2048 : 512) : ctx->cfg.top_nodes;
     if (topNodes > ctx->topNodesAvail) topNodes = ctx->topNodesAvail;
-    // the stack and, for SHARE, the queue area count as fixed bytes next to the staged nodes
-    size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int) + (SHARE ? sizeof(ShareArea) + (size_t)BLOCK * 16 + (size_t)BLOCK * 8 : 0);
+    size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int);
     // keep MIN_BLOCKS CTAs resident inside the 227 KB a CTA can opt into
     const size_t smemBudget = (size_t)(227 * 1024) / MIN_BLOCKS - 1024;
     topNodes &= ~7;                                  // planes stay 128-byte aligned
@@ -499,20 +316,20 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX = 0, bool SHARE = false>
+template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX = 0>
 static int launchFlags(b2rt_ctx* ctx, TraceParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS) {
         // the instrumented build always writes barycentrics (one kernel fewer to carry)
-        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX, SHARE>(ctx, p, stream)
-                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX, SHARE>(ctx, p, stream);
+        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
     }
-    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX, SHARE>(ctx, p, stream)
-                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX, SHARE>(ctx, p, stream);
-    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX, SHARE>(ctx, p, stream)
-                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX, SHARE>(ctx, p, stream);
+    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
+    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
 }
 
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
@@ -528,10 +345,16 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     p.topF4 = 0;
     p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
     p.nodeBreak = ctx->cfg.node_break <= 0 ? 0 : ctx->cfg.node_break;
+    {
+        // off unless asked for: measured on C2 (32 MB of BVH) it buys +0.3 % behind an L2 flush and costs 1-2 % when
+        // the arrays are already resident (profiles/README.md)
+        const bool on = ctx->cfg.l2_prefetch > 0;
+        p.pfNodeLines = on ? (int)std::min<size_t>(ctx->nodeBytes / 128, 1u << 20) : 0;
+        p.pfWoopLines = on ? (int)std::min<size_t>(ctx->woopBytes / 128, 1u << 20) : 0;
+    }
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.nodesTex = ctx->nodesTex; p.woopTex = ctx->woopTex;
-    p.dummyLeaf = ~(int)(ctx->woopBytes / 16);       // first padding row: a terminator (api.cu:b2rt_set_bvh)
     if (flags & B2RT_TRACE_STATS) {
         B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
         B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev + 8, 0xff, 2 * sizeof(unsigned long long), stream));    // minima
@@ -557,10 +380,6 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     case 7: return launchFlags<12, 512, 2>(ctx, p, flags, stream);   // two CTAs per SM, <= 64 regs
     case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // v6 with nodes through the texture pipe
     case 9: return launchFlags<12, 1024, 1, 2>(ctx, p, flags, stream);  // v6 with Woop rows through the texture pipe
-    case 10: return launchFlags<12, 1024, 1, 4>(ctx, p, flags, stream);  // v6 + cost probe: extra node load
-    case 11: return launchFlags<12, 1024, 1, 8>(ctx, p, flags, stream);  // v6 + cost probe: extra ALU work per node
-    case 13: return launchFlags<12, 1024, 1, 0, true>(ctx, p, flags, stream);  // v6 + subtree sharing in the tail
-    case 14: return launchFlags<12, 256, 4, 0, true>(ctx, p, flags, stream);   // v1 + subtree sharing in the tail
     }
 }
 

@@ -73,7 +73,9 @@ typedef struct {
     uint64_t ns_mean_exit;      /* mean warp exit time */
     uint64_t ns_last_exit;      /* last warp exit = length of the launch; (last - mean) / last = idle tail */
     uint64_t ns_exit_p50, ns_exit_p90, ns_exit_p99;    /* percentiles of the per-warp exit times */
-    uint64_t shares;            /* stack entries handed to idle lanes after the pool ran dry (subtree sharing) */
+    /* the warp that left last: when it fetched its last rays, and the loop iterations it ran from then on --
+     * the launch cannot end before that one bundle's dependent chain of node and triangle steps has */
+    uint64_t ns_straggler_fetch, straggler_node_iters, straggler_tri_iters;
 } b2rt_trace_stats;
 
 /* Tunables of the traversal kernel; zero-initialise and override what you need. */
@@ -84,6 +86,8 @@ typedef struct {
     int blocks_per_sm;          /* persistent CTAs per SM; -1 = from occupancy */
     int variant;                /* kernel variant id; -1 = chosen from the batch size */
     int node_break;             /* leave the inner-node loop when fewer lanes than this are still in it; <= 0 = default */
+    int l2_prefetch;            /* 1: every launch starts by pulling the private BVH arrays into L2 (bulk reads instead of
+                                   cold misses on the rays' dependent chains); 0 or -1: off (no measured gain) */
 } b2rt_trace_config;
 
 /* ---- context ---------------------------------------------------------------------------- */

@@ -168,68 +168,6 @@ def test_wide_kernel_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     assert (got["id"][5::97] == -1).all() and (got["t"][5::97] == -1.0).all()
 
 
-@pytest.mark.parametrize("variant", [13, 14])
-@pytest.mark.parametrize("kind,ntris", [("interior", 30000), ("strands", 30000), ("knot", 40000)])
-@pytest.mark.parametrize("count", [1, 37, 4097, 0])
-def test_subtree_sharing_tail(b2rt, oracle, ctx, kind, ntris, variant, count):
-    """Variants with tail-of-launch subtree sharing (trace.cu SHARE): idle lanes traverse stack entries donated by busy
-    lanes and the hits are merged by min t.  Small batches run almost entirely in that mode.  Same acceptance rule
-    as every other variant, and bit-identical t, u, v to the plain kernel wherever the ids agree."""
-    scene = b2rt.Scene.generate(kind, ntris, 20260101)
-    bvh = b2rt.BVH(scene)
-    rays = _primary_rays(b2rt, oracle, scene, 256, 192).copy()
-    if count:
-        rays = rays[np.linspace(0, len(rays) - 1, count).astype(np.int64)].copy()
-    rays["tmax"][5::97] = -1.0
-    tracer = b2rt.CudaTracer(ctx)
-    tracer.writeBarycentrics = True
-    tracer.setBVH(b2rt.CudaBVH(bvh))
-    rb = b2rt.RayBuffer()
-    rb.setRays(rays)
-    try:
-        ctx.set_trace_config(variant=1)
-        tracer.traceBatch(rb)
-        plain = rb.getResults().copy()
-        ctx.set_trace_config(variant=variant)
-        tracer.traceBatch(rb)
-        got = rb.getResults().copy()
-    finally:
-        ctx.set_trace_config()
-    agree = ID_AGREE if len(rays) > 10000 else 0.97             # one exact tie in 37 rays is allowed
-    _check_closest(oracle, bvh.arrays(), rays, got, agree=agree)
-    same = got["id"] == plain["id"]
-    assert same.mean() >= agree
-    hit = same & (got["id"] >= 0)
-    assert (got["t"][hit] == plain["t"][hit]).all() and (got["padA"][hit] == plain["padA"][hit]).all()
-    assert (got["padB"][hit] == plain["padB"][hit]).all()
-    assert (got["id"][5::97] == -1).all()
-
-
-def test_subtree_sharing_any_hit(b2rt, oracle, ctx):
-    scene = b2rt.Scene.generate("interior", 30000, 3)
-    bvh = b2rt.BVH(scene)
-    tracer = b2rt.CudaTracer(ctx)
-    tracer.setBVH(b2rt.CudaBVH(bvh))
-    origin, m = b2rt.camera_matrices(scene.camera, 128, 96)
-    rg = b2rt.RayGen(1 << 21, ctx)
-    prim = b2rt.RayBuffer()
-    rg.primary(prim, origin, m, 128, 96, scene.camera["far"])
-    try:
-        for variant in (13, 14):
-            ctx.set_trace_config(variant=variant)
-            tracer.traceBatch(prim)
-            sec = b2rt.RayBuffer()
-            rg.ao(sec, prim, scene, 4, 1.5, True)               # any hit
-            tracer.traceBatch(sec)
-            rays, got = sec.getRays(), sec.getResults()
-            ref = oracle.trace_woop(bvh.arrays(), rays, any_hit=False)
-            assert ((got["id"] >= 0) == (ref["id"] >= 0)).mean() >= ID_AGREE
-            hit = got["id"] >= 0
-            assert (got["t"][hit] > 0).all() and (got["t"][hit] < 1.5).all()
-    finally:
-        ctx.set_trace_config()
-
-
 def test_wide_kernel_any_hit_and_secondary(b2rt, oracle, ctx):
     scene = b2rt.Scene.generate("interior", 30000, 3)
     bvh = b2rt.BVH(scene)

@@ -58,6 +58,7 @@ def main():
             if tok.startswith("f"): kw["fetch_threshold"] = int(tok[1:])
             if tok.startswith("b"): kw["blocks_per_sm"] = int(tok[1:])
             if tok.startswith("n"): kw["node_break"] = int(tok[1:])
+            if tok.startswith("p"): kw["l2_prefetch"] = int(tok[1:])
         ctx.set_trace_config(**kw)
         ms = median_ms(frame.trace_all)
         out[s] = counted / ms / 1e3
@@ -68,10 +69,11 @@ def main():
             for rb, _ in frame.batches[:2]:
                 frame.tracer.traceBatch(rb)
                 st = frame.tracer.getStats()
-                print("    stats: TRV %.1f%% IST %.1f%% fetches %d shares %d | warps %d pool empty %.1f us, warp exit mean %.1f p50 %.1f p90 %.1f p99 %.1f last %.1f us" % (
-                    100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]), 100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"], st["shares"],
+                print("    stats: TRV %.1f%% IST %.1f%% fetches %d | warps %d pool empty %.1f us, warp exit mean %.1f p50 %.1f p90 %.1f p99 %.1f last %.1f us"
+                      " | last warp: last fetch at %.1f us, then %d node + %d triangle iterations" % (
+                    100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]), 100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"],
                     st["warps"], st["ns_pool_empty"] / 1e3, st["ns_mean_exit"] / 1e3, st["ns_exit_p50"] / 1e3, st["ns_exit_p90"] / 1e3,
-                    st["ns_exit_p99"] / 1e3, st["ns_last_exit"] / 1e3))
+                    st["ns_exit_p99"] / 1e3, st["ns_last_exit"] / 1e3, st["ns_straggler_fetch"] / 1e3, st["straggler_node_iters"], st["straggler_tri_iters"]))
             frame.tracer.collectStats = False
     ctx.set_trace_config()
     frame.trace_all()
