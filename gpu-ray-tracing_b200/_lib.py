@@ -34,7 +34,7 @@ class WorkCounters(C.Structure):
 
 
 class TraceConfig(C.Structure):
-    _fields_ = [("top_nodes", C.c_int), ("fetch_threshold", C.c_int), ("blocks_per_sm", C.c_int), ("variant", C.c_int), ("node_break", C.c_int), ("l2_prefetch", C.c_int)]
+    _fields_ = [("top_nodes", C.c_int), ("fetch_threshold", C.c_int), ("blocks_per_sm", C.c_int), ("variant", C.c_int), ("l2_prefetch", C.c_int)]
 
 
 class BuildParams(C.Structure):

@@ -49,7 +49,7 @@ struct b2rt_ctx {
     int wideNumNodes = 0, wideNumTris = 0;
     bool hasWide = false;
 
-    b2rt_trace_config cfg = { -1, -1, -1, -1, -1, -1 };
+    b2rt_trace_config cfg = { -1, -1, -1, -1, -1 };
 
     int* warpCounter = nullptr;                 // work counter for persistent warps
     unsigned long long* statsDev = nullptr;     // 16 counters for the instrumented kernel + kTimelineWarps exit times

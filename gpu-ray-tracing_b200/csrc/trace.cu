@@ -31,7 +31,6 @@ struct TraceParams {
     int numRays;
     int topF4;              // float4 elements of the node array staged in shared memory
     int fetchThreshold;
-    int nodeBreak;          // leave the node loop when fewer lanes than this are in it (0 = never)
     int pfNodeLines, pfWoopLines;   // 128-byte lines of the node / Woop arrays to pull into L2 when the launch starts (0 = none)
     int* warpCounter;
     unsigned long long* stats;
@@ -151,7 +150,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
         }
         if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break;     // warp out of work
 
-        const int nodeBreak = poolEmpty ? 0 : p.nodeBreak;
         const int threshold = poolEmpty ? 0 : p.fetchThreshold;
 
         // ---- traversal --------------------------------------------------------------------
@@ -200,17 +198,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                         push(c1);
                     }
                 }
-                // first leaf: postpone it and keep traversing
+                // first leaf: postpone it and keep traversing (measured: folding the two pops into one site, with the popped
+                // leaf postponed after the loop, costs 4 % on the diffuse batch -- the lane stops speculating earlier)
                 if (nodeAddr < 0 && leafAddr >= 0) {
                     leafAddr = nodeAddr;
                     nodeAddr = pop();
                 }
                 // every lane still here holds a leaf -> go intersect
-                {
-                    const unsigned am = __activemask();
-                    if (!__any_sync(am, leafAddr >= 0)) break;
-                    if (__popc(am) < nodeBreak) break;
-                }
+                if (!__any_sync(__activemask(), leafAddr >= 0)) break;
             }
 
             // postponed leaves
@@ -344,7 +339,6 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     p.numRays = (int)numRays;
     p.topF4 = 0;
     p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
-    p.nodeBreak = ctx->cfg.node_break <= 0 ? 0 : ctx->cfg.node_break;
     {
         // off unless asked for: measured on C2 (32 MB of BVH) it buys +0.3 % behind an L2 flush and costs 1-2 % when
         // the arrays are already resident (profiles/README.md)
@@ -365,6 +359,10 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // the tree wins on frame-sized batches (shorter tail, more node visits served from shared memory); four
         // 256-thread CTAs win on multi-million-ray batches
         variant = (numRays <= (4 << 20)) ? 6 : 1;
+        // a BVH several times the size of L2 (126 MB): most node visits go to DRAM, and the 8-wide compressed private form
+        // (80 bytes per 8 children instead of 64 per 2, trace_wide.cu) wins -- C4, 1.2 GB of Compact2 arrays: 500 vs 425
+        // Mrays/s.  It is built on first use (host collapse of the private copy, api.cu:ensureWide).
+        if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 104;
     }
     if (variant >= 8 && variant <= 9 && (!ctx->nodesTex || !ctx->woopTex)) variant = 6;   // array too large for a 1D texture
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);

@@ -85,7 +85,6 @@ typedef struct {
                                    (kepler_dynamic_fetch.cu:48 uses 20); -1 = default */
     int blocks_per_sm;          /* persistent CTAs per SM; -1 = from occupancy */
     int variant;                /* kernel variant id; -1 = chosen from the batch size */
-    int node_break;             /* leave the inner-node loop when fewer lanes than this are still in it; <= 0 = default */
     int l2_prefetch;            /* 1: every launch starts by pulling the private BVH arrays into L2 (bulk reads instead of
                                    cold misses on the rays' dependent chains); 0 or -1: off (no measured gain) */
 } b2rt_trace_config;

@@ -57,7 +57,6 @@ def main():
             if tok.startswith("t"): kw["top_nodes"] = int(tok[1:])
             if tok.startswith("f"): kw["fetch_threshold"] = int(tok[1:])
             if tok.startswith("b"): kw["blocks_per_sm"] = int(tok[1:])
-            if tok.startswith("n"): kw["node_break"] = int(tok[1:])
             if tok.startswith("p"): kw["l2_prefetch"] = int(tok[1:])
         ctx.set_trace_config(**kw)
         ms = median_ms(frame.trace_all)
@@ -69,6 +68,10 @@ def main():
             for rb, _ in frame.batches[:2]:
                 frame.tracer.traceBatch(rb)
                 st = frame.tracer.getStats()
+                if st["warps"] == 0:        # the wide kernel keeps the SIMD counters only
+                    print("    stats: TRV %.1f%% IST %.1f%% fetches %d" % (100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]),
+                                                                         100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"]))
+                    continue
                 print("    stats: TRV %.1f%% IST %.1f%% fetches %d | warps %d pool empty %.1f us, warp exit mean %.1f p50 %.1f p90 %.1f p99 %.1f last %.1f us"
                       " | last warp: last fetch at %.1f us, then %d node + %d triangle iterations" % (
                     100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]), 100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"],
