@@ -81,6 +81,7 @@ _SIGNATURES = {
     "b2rt_bvh_save": (i32, [vp, C.c_char_p]),
     "b2rt_bvh_load": (i32, [C.c_char_p, C.POINTER(vp)]),
     "b2rt_tri_normals": (i32, [vp, vp, i32, vp]),
+    "b2rt_woopify": (i32, [vp, vp, vp, vp, vp, i64, vp, i64, vp]),
     "b2rt_wide_build": (i32, [vp, sz, vp, sz, vp, sz, C.POINTER(vp)]),
     "b2rt_wide_free": (None, [vp]),
     "b2rt_wide_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), vp]),

@@ -31,6 +31,7 @@ CUDA_SOURCES = [
     ("raygen.cu", ["-fmad=false"]),
     ("raysort.cu", ["-fmad=false"]),
     ("misc.cu", ["-fmad=false"]),
+    ("woopify.cu", ["-fmad=false"]),
 ]
 HOST_SOURCES = ["host/bvh_builder.cpp", "host/scenegen.cpp", "host/host_util.cpp", "host/wide_bvh.cpp"]
 HOST_FLAGS = ["-O2", "-ffp-contract=off", "-fPIC", "-std=c++17", "-pthread", "-Wall", "-I", INCLUDE]

@@ -210,6 +210,20 @@ class CudaBVH:
         self.m_triWoop = torch.from_numpy(np.ascontiguousarray(arrays["woop"], np.float32).copy()).to(self.device)
         self.m_triIndex = torch.from_numpy(np.ascontiguousarray(arrays["triIndex"], np.int32).copy()).to(self.device)
 
+    @classmethod
+    def fromSceneOnDevice(cls, scene, arrays, ctx=None, device=None):
+        """Upload nodes and triIndex, compute the Woop rows ON the device from the scene's vertices (b2rt_woopify;
+        replaces the woopifyTri loop of CudaBVH::createCompact, CudaBVH.cc:270-380).  `arrays` needs nodes and
+        triIndex only; the rows come out bit-identical to the host-built ones."""
+        self = cls.__new__(cls)
+        self.m_layout = int(arrays.get("layout", LAYOUT_COMPACT2))
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        ctx = ctx or Context.get(self.device.index)
+        self.m_nodes = torch.from_numpy(np.ascontiguousarray(arrays["nodes"], np.float32).copy()).to(self.device)
+        self.m_triIndex = torch.from_numpy(np.ascontiguousarray(arrays["triIndex"], np.int32).copy()).to(self.device)
+        self.m_triWoop = woopify_device(scene, arrays["nodes"], arrays["triIndex"], ctx, self.device)
+        return self
+
     def getLayout(self):
         return self.m_layout
 
@@ -221,6 +235,40 @@ class CudaBVH:
 
     def getTriIndexBuffer_dev(self):
         return self.m_triIndex
+
+
+def leaf_references(nodes, triIndex):
+    """(first row, triangle) of every triangle reference of a Compact2 BVH, from the node array's leaf pointers: a
+    negative child index is ~(first row of the leaf) (CudaBVH.cc:300-330), a leaf is 3 rows per triangle plus one
+    terminator row, so the gaps between consecutive leaf starts give the triangle counts."""
+    n = np.ascontiguousarray(nodes, np.float32).view(np.int32).reshape(-1, 16)
+    tri = np.ascontiguousarray(triIndex, np.int32).reshape(-1)
+    child = n[:, 12:14].reshape(-1)
+    starts = np.unique(~child[child < 0]).astype(np.int64)
+    ends = np.append(starts[1:], len(tri))              # one past the leaf's terminator row
+    counts = (ends - starts - 1) // 3
+    if ((ends - starts - 1) % 3 != 0).any() or (counts < 0).any():
+        raise ValueError("leaf_references: leaf rows are not 3 per triangle + 1 terminator")
+    leaf_of_ref = np.repeat(np.arange(len(starts)), counts)
+    within = np.arange(int(counts.sum())) - np.repeat(np.cumsum(counts) - counts, counts)
+    rows = (starts[leaf_of_ref] + 3 * within).astype(np.int32)
+    return rows, tri[rows].astype(np.int32)
+
+
+def woopify_device(scene, nodes, triIndex, ctx=None, device=None):
+    """b2rt_woopify: device tensor of len(triIndex) Woop rows (4 floats each) for the scene's triangles."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    ctx = ctx or Context.get(device.index)
+    rows, tris = leaf_references(nodes, triIndex)
+    num_rows = int(np.asarray(triIndex).size)
+    verts_d = torch.from_numpy(np.ascontiguousarray(scene.verts, np.float32).reshape(-1).copy()).to(device)
+    index_d = torch.from_numpy(np.ascontiguousarray(scene.tris, np.int32).reshape(-1).copy()).to(device)
+    rows_d = torch.from_numpy(rows).to(device)
+    tris_d = torch.from_numpy(tris).to(device)
+    woop = torch.empty(num_rows * 4, dtype=torch.float32, device=device)
+    check(lib().b2rt_woopify(ctx.handle, _dptr(verts_d), _dptr(index_d), _dptr(rows_d), _dptr(tris_d), len(rows), _dptr(woop),
+                             num_rows, _stream_ptr()), ctx.handle)
+    return woop
 
 
 # ---------------------------------------------------------------------------------------------
@@ -627,6 +675,26 @@ def reconstruct(mode, numRaysPerPrimary, firstPrimary, numPrimary, primaryRays, 
                                  _dptr(primaryRays.m_slotToID), _dptr(primaryRays.m_results), _dptr(batchRays.m_IDToSlot),
                                  _dptr(batchRays.m_results), _dptr(triMaterialColor_dev), _dptr(triShadedColor_dev),
                                  _dptr(pixels_dev), _stream_ptr()), ctx.handle)
+
+
+def save_image(pixels, width, height, path, flip=True):
+    """Headless stand-in for the reference's display path (App.cc:62-132 draws the pixel buffer with glDrawPixels:
+    unavailable on this box): write the U32 ABGR frame that `reconstruct` fills (RendererKernels.cu:60-108, byte 0 =
+    red) as a binary PPM.  glDrawPixels puts row 0 at the BOTTOM of the window, so rows are written last-first unless
+    flip=False.  `pixels` is a device or host tensor / array of width*height 32-bit words.  Returns the RGB array."""
+    if hasattr(pixels, "detach"):
+        pixels = pixels.detach().cpu().numpy()
+    px = np.ascontiguousarray(pixels).view(np.uint32).reshape(-1)
+    if px.size != width * height:
+        raise ValueError("save_image: %d pixels for a %dx%d frame" % (px.size, width, height))
+    rgb = px.view(np.uint8).reshape(height, width, 4)[:, :, :3]
+    if flip:
+        rgb = rgb[::-1]
+    rgb = np.ascontiguousarray(rgb)
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (width, height))
+        f.write(rgb.tobytes())
+    return rgb
 
 
 # ---------------------------------------------------------------------------------------------

@@ -216,6 +216,13 @@ int  b2rt_bvh_save(const b2rt_host_bvh* bvh, const char* path);
 int  b2rt_bvh_load(const char* path, b2rt_host_bvh** out);
 /* per-triangle normals as Scene does (rt/Scene.cc:72) */
 int  b2rt_tri_normals(const float* verts, const int32_t* tris, int num_tris, float* normals);
+/* The Woop rows of a Compact2 BVH computed on the device: replaces the per-triangle part of CudaBVH::createCompact /
+ * woopifyTri (CudaBVH.cc:270-380; matrix inverse of Math.hh:935-983), bit-identical to the host computation.
+ * All pointers are device memory.  verts: xyz per vertex; vtx_index: three vertex indices per triangle; reference r
+ * (r < num_refs) is triangle ref_tri[r] and occupies rows ref_row[r] .. ref_row[r]+2 of `woop` (num_rows 16-byte rows);
+ * every row no reference covers becomes a leaf terminator (x = 0x80000000, CudaBVH.hh:47-50). */
+int  b2rt_woopify(b2rt_ctx* ctx, const float* verts, const int32_t* vtx_index, const int32_t* ref_row, const int32_t* ref_tri,
+                  int64_t num_refs, void* woop, int64_t num_rows, void* stream);
 
 /* Private 8-wide compressed form of a Compact2 BVH (csrc/wide_bvh.h): what b2rt_set_bvh builds for the wide
  * traversal kernel (b2rt_trace_config.variant >= 100), exposed so it can be built and inspected without a GPU.

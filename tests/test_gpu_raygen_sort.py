@@ -158,3 +158,29 @@ def test_count_hits_and_reconstruct(b2rt, oracle, ctx):
         ref[:] = 0
         oracle.reconstruct(4, 0, w * h, mode, s2i, res, sec.getIDToSlotBuffer_dev().cpu().numpy(), sres, mat, shd, ref)
         assert (pix.cpu().numpy().view(np.uint32) == ref).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,target", [("blob", 20000), ("interior", 30000), ("strands", 30000), ("knot", 40000)])
+def test_device_woopify_is_bit_identical(b2rt, oracle, ctx, kind, target):
+    """the Woop rows computed on the device (b2rt_woopify) equal the host-built ones bit for bit
+    -- and therefore the oracle's woopifyTri restatement, which pins the host builder (test_host_logic)."""
+    import torch
+    scene = b2rt.Scene.generate(kind, target, 20260101)
+    bvh = b2rt.BVH(scene)
+    a = bvh.arrays()
+    dev = b2rt.CudaBVH.fromSceneOnDevice(scene, {"nodes": a["nodes"], "triIndex": a["triIndex"]}, ctx)
+    got = dev.getTriWoopBuffer_dev().cpu().numpy().view(np.uint32)
+    ref = np.ascontiguousarray(a["woop"], np.float32).reshape(-1).view(np.uint32)
+    assert got.shape == ref.shape
+    assert (got == ref).all(), "%d of %d words differ" % ((got != ref).sum(), ref.size)
+    # and the tracer accepts it like any other CudaBVH
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.setBVH(dev)
+    origin, m = b2rt.camera_matrices(scene.camera, 64, 48)
+    rg = b2rt.RayGen(1 << 20, ctx)
+    prim = b2rt.RayBuffer()
+    rg.primary(prim, origin, m, 64, 48, scene.camera["far"])
+    tracer.traceBatch(prim)
+    ref_hits = oracle.trace_woop(a, prim.getRays())
+    assert (prim.getResults()["id"] == ref_hits["id"]).mean() >= 0.999

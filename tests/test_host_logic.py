@@ -154,3 +154,44 @@ def test_shard_range(b2rt):
             assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
             sizes = [b - a for a, b in parts]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_save_image_ppm(b2rt, tmp_path):
+    """Row f1's headless image write: ABGR words -> binary PPM, bottom row first in memory (glDrawPixels convention)."""
+    w, h = 5, 3
+    px = np.zeros(w * h, dtype=np.uint32)
+    px[0] = 0xFF0000FF           # red, bottom-left in the reference's window
+    px[w * h - 1] = 0xFFFF0000   # blue, top-right
+    px[w] = 0xFF00FF00           # green, second row from the bottom, left
+    path = tmp_path / "frame.ppm"
+    rgb = b2rt.save_image(px, w, h, str(path))
+    raw = path.read_bytes()
+    header = b"P6\n5 3\n255\n"
+    assert raw.startswith(header) and len(raw) == len(header) + w * h * 3
+    img = np.frombuffer(raw[len(header):], dtype=np.uint8).reshape(h, w, 3)
+    assert (img == rgb).all()
+    assert tuple(img[h - 1, 0]) == (255, 0, 0)        # bottom-left
+    assert tuple(img[0, w - 1]) == (0, 0, 255)        # top-right
+    assert tuple(img[h - 2, 0]) == (0, 255, 0)
+    with pytest.raises(ValueError):
+        b2rt.save_image(px[:-1], w, h, str(path))
+
+
+@pytest.mark.parametrize("kind,target", [("blob", 3000), ("strands", 6000)])
+def test_leaf_references_cover_every_triangle_row(b2rt, kind, target):
+    """Input of the device Woop transform (b2rt_woopify): the (row, triangle) list recovered from the node array's leaf
+    pointers names exactly the non-terminator rows of the host-built array, three rows apart inside a leaf."""
+    scene = b2rt.Scene.generate(kind, target, 11)
+    bvh = b2rt.BVH(scene)               # arrays() are views into the builder's memory: keep it alive
+    a = bvh.arrays()
+    rows, tris = b2rt.leaf_references(a["nodes"], a["triIndex"])
+    woop = np.ascontiguousarray(a["woop"], np.float32).view(np.uint32).reshape(-1, 4)
+    covered = np.zeros(len(woop), bool)
+    for k in range(3):
+        assert not covered[rows + k].any()
+        covered[rows + k] = True
+    term = ~covered
+    assert (woop[term] == 0x80000000).all(), "rows outside the references are the leaf terminators"
+    assert (woop[rows, 0] != 0x80000000).all()
+    assert (tris == np.asarray(a["triIndex"])[rows]).all() and tris.min() >= 0 and tris.max() < len(scene.tris)
+    assert len(rows) >= len(scene.tris)         # spatial splits only add references
