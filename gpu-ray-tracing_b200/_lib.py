@@ -26,7 +26,7 @@ class B2rtError(RuntimeError):
 
 class TraceStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("node_iters", "node_lanes", "tri_iters", "tri_lanes", "fetches", "rays", "warps", "ns_pool_empty",
-                                           "ns_mean_exit", "ns_last_exit", "ns_exit_p50", "ns_exit_p90", "ns_exit_p99", "ns_straggler_fetch", "straggler_node_iters", "straggler_tri_iters")]
+                                           "ns_mean_exit", "ns_last_exit", "ns_exit_p50", "ns_exit_p90", "ns_exit_p99", "ns_straggler_fetch", "straggler_node_iters", "straggler_tri_iters", "shares")]
 
 
 class WorkCounters(C.Structure):

@@ -175,7 +175,7 @@ void b2rt_destroy(b2rt_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaFree(ctx->nodes); cudaFree(ctx->woop); cudaFree(ctx->triIndex);
     cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
-    cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch); cudaFree(ctx->stage);
+    cudaFree(ctx->shareList); cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch); cudaFree(ctx->stage);
     cudaFree(ctx->aabbDev); cudaFree(ctx->countDev);
     if (ctx->nodesTex) cudaDestroyTextureObject(ctx->nodesTex);
     if (ctx->woopTex) cudaDestroyTextureObject(ctx->woopTex);
@@ -232,7 +232,8 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     // Woop rows: the leaf loop fetches three rows before it looks at the terminator, so the copy
     // carries padding rows past the last terminator (the reference relies on texture fetches
     // returning zero out of range, kepler_dynamic_fetch.cu:328-334).  The first padding row is
-    // itself a terminator, so a leaf loop that runs off a malformed last leaf stops there.
+    // itself a terminator: row woopBytes/16 is a leaf without triangles, which the any-hit kernel leaves
+    // in place of stack entries it hands to other lanes (trace.cu, SHARE).
     const cudaMemcpyKind kind = srcIsDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     B2RT_CUDA(ctx, cudaMalloc(&ctx->woop, woopBytes + kWoopPadBytes));
     B2RT_CUDA(ctx, cudaMemset(reinterpret_cast<char*>(ctx->woop) + woopBytes, 0, kWoopPadBytes));
@@ -391,6 +392,7 @@ int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out)
     out->ns_pool_empty = out->ns_mean_exit = out->ns_last_exit = 0;
     out->ns_exit_p50 = out->ns_exit_p90 = out->ns_exit_p99 = 0;
     out->ns_straggler_fetch = out->straggler_node_iters = out->straggler_tri_iters = 0;
+    out->shares = h[13];
     if (h[12] && h[8] != ~0ull) {
         const unsigned long long start40 = h[8] & 0xffffffffffull;
         out->ns_last_exit = h[11] - h[8];

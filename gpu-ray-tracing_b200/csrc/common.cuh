@@ -62,6 +62,7 @@ struct b2rt_ctx {
     // scratch (grown on demand, never shrunk)
     void* scratch = nullptr;  size_t scratchBytes = 0;
     void* stage = nullptr;    size_t stageBytes = 0;   // device staging for b2rt_trace_host
+    int* shareList = nullptr; size_t shareListCtas = 0; // any-hit kernels: shared-ray lists, one slice per CTA (trace.cu)
     float* aabbDev = nullptr;                   // 6 floats
     long long* countDev = nullptr;              // hit counter
 };

@@ -31,6 +31,8 @@ struct TraceParams {
     int numRays;
     int topF4;              // float4 elements of the node array staged in shared memory
     int fetchThreshold;
+    int dummyLeaf;          // ~row of the terminator row behind the caller's Woop rows: a leaf without triangles (SHARE)
+    int* shareList;         // SHARE: kShareList ray indices per CTA
     int pfNodeLines, pfWoopLines;   // 128-byte lines of the node / Woop arrays to pull into L2 when the launch starts (0 = none)
     int* warpCounter;
     unsigned long long* stats;
@@ -43,6 +45,28 @@ constexpr unsigned kFull = 0xffffffffu;
 // TEX bit 0: node fetches outside the shared-memory top go through the texture pipe; bit 1: Woop rows do.
 // The L1 data is the same, but texture fetches use l1tex's TEX data pipe instead of the LSU data pipe that
 // ncu shows near saturation (l1tex__data_pipe_lsu_wavefronts 69-74 % of peak on the diffuse batch).
+// SHARE (compiled into the ANY_HIT kernels): subtree sharing in the tail of a launch.  Once the work counter has run dry a
+// launch is a set of dependent chains -- every remaining ray needs its remaining node visits one after the other, ~380 ns
+// each -- while most lanes and warps of the SM have nothing left to do (C3 AO batches: pool empty at 285 us, last warp at
+// 440 us).  An any-hit ray that misses (96 % of C3's) has to visit EVERY entry of its stack, so the entries are real,
+// independent work: lanes that are still traversing hand the LOWEST entries of their stacks -- whole subtrees -- to a
+// queue in shared memory; idle lanes of any warp of the CTA take them, re-read the ray, traverse the subtree and merge a
+// hit into the ray's result record with a 64-bit atomicMin on (t, Woop row).  After the CTA's last warp has left the loop
+// the CTA rewrites the records of its shared rays into the final form (triangle id, barycentrics).  Nothing waits on
+// anything but the queue's try-lock.  Closest-hit kernels do not share: front to back, the old stack entries are far
+// subtrees the owner culls once it has its hit, and handing them over bought nothing.
+struct ShareArea {
+    int lock;               // 0 free, 1 taken (try-lock; idle warps retry, busy warps just skip the visit)
+    int head, tail;         // queue positions, free-running; changed under the lock
+    int idleWarps;          // warps of the CTA without a ray in flight (includes warps that have left)
+    int listCount;          // shared rays of this CTA (entries of its slice of TraceParams::shareList)
+    int pad[3];
+};
+constexpr int kShareSteps = 4;      // tail of the launch: node steps between two visits of the queue
+constexpr int kShareRounds = 4;     // stack entries a lane may hand over per visit
+constexpr int kShareQueue = 128;    // queue entries (int4: ray, stack entry, hit distance); 2 KB keeps the L1 carve-out where it was
+constexpr int kShareList = 4096;    // shared rays per CTA (global memory)
+
 template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
@@ -74,6 +98,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             else s_child[node] = make_int2(__float_as_int(v.x), __float_as_int(v.y));
         }
     }
+    // SHARE: [ShareArea][queue] behind the planes
+    constexpr bool SHARE = ANY_HIT;
+    constexpr int kQueue = kShareQueue, kListCap = kShareList, kWarps = BLOCK / 32;
+    ShareArea* s_share = reinterpret_cast<ShareArea*>(reinterpret_cast<char*>(s_plane) + (size_t)topNodes * 56);
+    int4* s_queue = reinterpret_cast<int4*>(s_share + 1);
+    int* s_list = p.shareList + (size_t)blockIdx.x * kListCap;
+    if (SHARE && threadIdx.x == 0) { s_share->lock = 0; s_share->head = 0; s_share->tail = 0; s_share->idleWarps = 0; s_share->listCount = 0; }
     __syncthreads();
     unsigned sTop = (unsigned)__cvta_generic_to_shared(s_plane);              // 32-bit shared address of plane 0
     asm volatile("mov.u32 %0, %0;" : "+r"(sTop));      // opaque: keep it in a register instead of re-deriving it per node
@@ -93,12 +124,18 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
     int sp = 0;                         // number of entries held in memory
     bool poolEmpty = false;             // warp-uniform: the work counter ran past numRays
 
+    // subtree sharing (SHARE)
+    bool viaAtomic = false;             // this lane's ray is shared (or the lane works on a handed-over subtree): merge by atomicMin
+    int giveSlot = 2;                   // lowest stack slot not yet handed over (slots 0 and 1 hold the sentinel)
+    bool countedIdle = false;           // warp-uniform: this warp is counted in ShareArea::idleWarps
+
     unsigned long long stNodeIters = 0, stNodeLanes = 0, stTriIters = 0, stTriLanes = 0, stFetches = 0;
-    unsigned long long stStart = 0, stPoolEmpty = 0, stLastFetch = 0, stItersAtFetch = 0;
+    unsigned long long stStart = 0, stPoolEmpty = 0, stShares = 0, stLastFetch = 0, stItersAtFetch = 0;
     if (STATS) stStart = globalTimerNs();
 
     auto warpSum = [&](unsigned long long v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o); return v; };
     auto stackStore = [&](int slot, int v) {
+
         if (slot < STACK_SMEM) s_stack[slot * BLOCK] = v; else lstack[slot - STACK_SMEM] = v;
     };
     auto stackLoad = [&](int slot) -> int {
@@ -112,12 +149,27 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
         // ---- store finished rays, refill -------------------------------------------------
         const bool terminated = (nodeAddr == kSentinel);
         if (terminated && rayidx >= 0) {
-            const int id = (hitIndex == -1) ? -1 : __ldg(p.triIndex + hitIndex);
-            if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
-            else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
+            if (SHARE && viaAtomic) {
+                // shared ray: (t, Woop row) competes with what the other lanes working on this ray found
+                if (hitIndex != -1)
+                    atomicMin(reinterpret_cast<unsigned long long*>(p.results + rayidx),
+                              ((unsigned long long)__float_as_uint(hitT) << 32) | (unsigned)hitIndex);
+            } else {
+                const int id = (hitIndex == -1) ? -1 : __ldg(p.triIndex + hitIndex);
+                if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
+                else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
+            }
             rayidx = -1;
         }
         const unsigned maskT = __ballot_sync(kFull, terminated);
+        // A warp of this CTA without work means the pool is empty: start visiting the queue.  poolEmpty has to stay
+        // warp-uniform (it guards full-mask shuffles) and the lanes need not have reconverged after the stores above, so
+        // they could see different values of the counter: lane 0 reads, everybody takes its answer.
+        if (SHARE && !poolEmpty) {
+            int idle = 0;
+            if (lane == 0) idle = *reinterpret_cast<volatile int*>(&s_share->idleWarps);
+            if (__shfl_sync(kFull, idle, 0) > 0) poolEmpty = true;
+        }
         if (maskT != 0 && !poolEmpty) {
             const int numT = __popc(maskT);
             const int leader = __ffs(maskT) - 1;
@@ -145,16 +197,131 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     stackStore(0, kSentinel);
                     sp = 1; tos = kSentinel;
                     leafAddr = 0; nodeAddr = 0; hitIndex = -1;
+                    if (SHARE) { giveSlot = 2; viaAtomic = false; }
                 }
             }
         }
-        if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break;     // warp out of work
+        if (SHARE && poolEmpty) {
+            bool leave = false;
+            for (;;) {
+                const bool busy = (nodeAddr != kSentinel);
+                const unsigned busyMask = __ballot_sync(kFull, busy);
+                const unsigned idleMask = ~busyMask;
+                // hand over only from rays whose t is a positive float (its bits then order like the value)
+                if (giveSlot > sp) giveSlot = max(sp, 2);           // the stack has shrunk below entries handed over earlier
+                const bool canGive = busy && sp > giveSlot && tmin >= 0.0f;
+                const unsigned giveMask = __ballot_sync(kFull, canGive);
+                volatile ShareArea* sh = s_share;
+                // hints, read by lane 0 for the whole warp (every decision below has to be warp-uniform); the exact
+                // values are read under the lock
+                int qLen = 0, idleW = 0;
+                if (lane == 0) { qLen = sh->tail - sh->head; idleW = sh->idleWarps; }
+                qLen = __shfl_sync(kFull, qLen, 0); idleW = __shfl_sync(kFull, idleW, 0);
+                const bool wantPop = idleMask != 0 && qLen > 0;
+                const bool wantPush = giveMask != 0 && qLen < kQueue / 2 && (idleMask != 0 || idleW > 0);
+                if (wantPop || wantPush) {
+                    int got = 0;
+                    if (lane == 0) got = (atomicCAS(&s_share->lock, 0, 1) == 0);
+                    got = __shfl_sync(kFull, got, 0);
+                    if (got) {
+                        __threadfence_block();
+                        int h = 0, t = 0, listCount = 0;
+                        if (lane == 0) { h = sh->head; t = sh->tail; listCount = sh->listCount; }
+                        h = __shfl_sync(kFull, h, 0); t = __shfl_sync(kFull, t, 0); listCount = __shfl_sync(kFull, listCount, 0);
+                        const unsigned below = (1u << lane) - 1u;
+                        if (wantPush) {
+                            // Up to kShareRounds entries per lane and visit, lowest first: with most of the SM idle the
+                            // subtrees should fan out as fast as the queue takes them.
+                            bool anyFresh = false;
+                            for (int round = 0; round < kShareRounds; round++) {
+                                const bool give = busy && sp > giveSlot && tmin >= 0.0f;
+                                // lanes whose ray is not shared yet also need a slot in the CTA's list of shared rays
+                                const bool needList = give && !viaAtomic;
+                                const unsigned needMask = __ballot_sync(kFull, needList);
+                                const bool listOk = !needList || listCount + __popc(needMask & below) < kListCap;
+                                const unsigned okMask = __ballot_sync(kFull, give && listOk);
+                                const int space = kQueue - (t - h);
+                                if (okMask == 0 || space <= 0) break;
+                                const int rank = __popc(okMask & below);
+                                bool fresh = false;
+                                if (give && listOk && rank < space) {
+                                    if (!viaAtomic) {
+                                        s_list[listCount + __popc(needMask & below)] = rayidx;
+                                        *reinterpret_cast<unsigned long long*>(p.results + rayidx) = ~0ull;     // "nothing found yet"
+                                        viaAtomic = true; fresh = true;
+                                    }
+                                    const int entry = stackLoad(giveSlot);
+                                    stackStore(giveSlot, p.dummyLeaf);
+                                    giveSlot++;
+                                    s_queue[(unsigned)(t + rank) % kQueue] = make_int4(rayidx, entry, __float_as_int(hitT), 0);
+                                    if (STATS) stShares++;
+                                }
+                                // (the lanes that give are the first ones in lane order, so the new list slots are contiguous)
+                                const unsigned gaveFresh = __ballot_sync(kFull, fresh);
+                                listCount += __popc(gaveFresh);
+                                anyFresh |= gaveFresh != 0;
+                                t += min(__popc(okMask), space);
+                            }
+                            if (anyFresh) __threadfence();          // the cleared records are in L2 before anybody can take the entries
+                            __syncwarp();
+                        }
+                        const int nPop = min(__popc(idleMask), t - h);
+                        const int prank = __popc(idleMask & below);
+                        int4 item = make_int4(-1, 0, 0, 0);
+                        if (!busy && prank < nPop) item = s_queue[(unsigned)(h + prank) % kQueue];
+                        __syncwarp();
+                        if (lane == 0) {
+                            sh->head = h + nPop; sh->tail = t; sh->listCount = listCount;
+                            if (nPop > 0 && countedIdle) atomicSub(&s_share->idleWarps, 1);
+                            __threadfence_block();
+                            atomicExch(&s_share->lock, 0);
+                        }
+                        if (nPop > 0) countedIdle = false;
+                        if (item.x >= 0) {
+                            // a handed-over subtree: the ray again, the hit distance of the moment it was handed over
+                            rayidx = item.x;
+                            const float4 o = ldg4(p.rays + 2 * (size_t)rayidx);
+                            const float4 d = ldg4(p.rays + 2 * (size_t)rayidx + 1);
+                            origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
+                            dirx = d.x; diry = d.y; dirz = d.z; hitT = __int_as_float(item.z);
+                            const float ooeps = 8.271806125530277e-25f;
+                            idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+                            idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+                            idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+                            oodx = origx * idirx; oody = origy * idiry; oodz = origz * idirz;
+                            hitIndex = -1; viaAtomic = true; giveSlot = 2;
+                            stackStore(0, kSentinel);
+                            sp = 1; tos = kSentinel;
+                            // an inner node starts the node loop; a leaf goes straight to the postponed slot, with the empty
+                            // leaf behind it so that the loops below run their usual course
+                            if (item.y >= 0) { nodeAddr = item.y; leafAddr = 0; } else { leafAddr = item.y; nodeAddr = p.dummyLeaf; }
+                        }
+                    }
+                }
+                if (__ballot_sync(kFull, nodeAddr != kSentinel) != 0) break;        // somebody has work: traverse
+                // the whole warp is idle: say so, then wait for entries or for everybody else to run dry as well
+                if (!countedIdle) {
+                    if (lane == 0) atomicAdd(&s_share->idleWarps, 1);
+                    countedIdle = true;
+                }
+                {
+                    int done = 0;
+                    if (lane == 0) done = (sh->tail - sh->head <= 0 && sh->idleWarps >= kWarps);
+                    if (__shfl_sync(kFull, done, 0)) { leave = true; break; }
+                }
+                __nanosleep(200);
+            }
+            if (leave) break;
+        }
+        if (!SHARE || !poolEmpty) { if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break; }     // warp out of work
 
-        const int threshold = poolEmpty ? 0 : p.fetchThreshold;
+        // after the pool is empty: without SHARE never leave the loop early; with SHARE come back up after every pass
+        const int threshold = poolEmpty ? (SHARE ? 33 : 0) : p.fetchThreshold;
 
         // ---- traversal --------------------------------------------------------------------
         while (nodeAddr != kSentinel) {
             // inner nodes, until every participating lane holds a postponed leaf
+            int tailSteps = kShareSteps;        // SHARE, pool empty: go back up for sharing every few node steps
             while ((unsigned)nodeAddr < (unsigned)kSentinel) {
                 if (STATS) { const unsigned am = __activemask(); stNodeLanes++; if (lane == __ffs(am) - 1) stNodeIters++; }
                 float4 n0xy, n1xy, nz;
@@ -206,6 +373,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                 }
                 // every lane still here holds a leaf -> go intersect
                 if (!__any_sync(__activemask(), leafAddr >= 0)) break;
+                if (SHARE && poolEmpty && --tailSteps == 0) break;
             }
 
             // postponed leaves
@@ -247,6 +415,39 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 
             // dynamic fetch: too few lanes left -> leave and refill the idle ones
             if (__popc(__activemask()) < threshold) break;
+            if (SHARE && !poolEmpty && *reinterpret_cast<volatile int*>(&s_share->idleWarps) > 0) break;
+        }
+    }
+
+    if (SHARE) {
+        // Every lane that worked on a shared ray of this CTA belongs to this CTA and has merged its hit.  Turn the merged
+        // (Woop row, t) records into the final form: triangle id through triIndex, barycentrics recomputed with the
+        // arithmetic of the leaf loop (same operands, same order: the same bits), t = tmax for a miss.
+        __syncthreads();
+        const int shared = s_share->listCount;
+        for (int i = threadIdx.x; i < shared; i += BLOCK) {
+            const int r = s_list[i];
+            const unsigned long long key = __ldcg(reinterpret_cast<const unsigned long long*>(p.results + r));
+            const int row = (int)(unsigned)(key & 0xffffffffull);
+            const float4 d = ldg4(p.rays + 2 * (size_t)r + 1);
+            int id = -1;
+            float t = d.w, u = 0.f, v = 0.f;
+            if (row != -1) {
+                id = __ldg(p.triIndex + row);
+                t = __uint_as_float((unsigned)(key >> 32));
+                if (BARY) {
+                    const float4 o = ldg4(p.rays + 2 * (size_t)r);
+                    const float4 v11 = ldg4(p.woop + row + 1), v22 = ldg4(p.woop + row + 2);
+                    const float Ox = __fmaf_rn(o.z, v11.z, __fmaf_rn(o.y, v11.y, __fmaf_rn(o.x, v11.x, v11.w)));
+                    const float Dx = __fmaf_rn(d.z, v11.z, __fmaf_rn(d.y, v11.y, __fmul_rn(d.x, v11.x)));
+                    u = __fmaf_rn(t, Dx, Ox);
+                    const float Oy = __fmaf_rn(o.z, v22.z, __fmaf_rn(o.y, v22.y, __fmaf_rn(o.x, v22.x, v22.w)));
+                    const float Dy = __fmaf_rn(d.z, v22.z, __fmaf_rn(d.y, v22.y, __fmul_rn(d.x, v22.x)));
+                    v = __fmaf_rn(t, Dy, Oy);
+                }
+            }
+            if (BARY) p.results[r] = make_int4(id, __float_as_int(t), __float_as_int(u), __float_as_int(v));
+            else reinterpret_cast<int2*>(p.results)[r * 2] = make_int2(id, __float_as_int(t));
         }
     }
 
@@ -259,6 +460,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             stTriIters += __shfl_xor_sync(kFull, stTriIters, o);
             stTriLanes += __shfl_xor_sync(kFull, stTriLanes, o);
             stFetches += __shfl_xor_sync(kFull, stFetches, o);
+            stShares += __shfl_xor_sync(kFull, stShares, o);
         }
         if (lane == 0) {
             atomicAdd(p.stats + 0, stNodeIters); atomicAdd(p.stats + 1, stNodeLanes);
@@ -271,6 +473,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             atomicAdd(p.stats + 10, now & 0xffffffffffull);     // low 40 bits: sums of <= 2^20 warps cannot overflow
             atomicMax(p.stats + 11, now);
             atomicAdd(p.stats + 12, 1ull);
+            atomicAdd(p.stats + 13, stShares);
             const int gw = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
             if (gw < kTimelineWarps) p.stats[16 + gw] = now;
             if (gw < kTimelineWarps) { p.stats[16 + kTimelineWarps + gw] = stLastFetch; p.stats[16 + 2 * kTimelineWarps + gw] = dbgIters - stItersAtFetch; }
@@ -287,9 +490,12 @@ template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MI
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
     auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>;
-    int topNodes = ctx->cfg.top_nodes < 0 ? (BLOCK >= 1024 ? 2048 : 512) : ctx->cfg.top_nodes;
+    // any-hit kernels carry the sharing queue behind the staged nodes; the small-CTA default gives up 40 nodes for it so
+    // that four CTAs still fit the 164 KB shared-memory step (the next step, 196 KB, costs 32 KB of L1)
+    constexpr size_t shareBytes = ANY_HIT ? sizeof(ShareArea) + (size_t)kShareQueue * sizeof(int4) : 0;
+    int topNodes = ctx->cfg.top_nodes < 0 ? (BLOCK >= 1024 ? 2048 : (ANY_HIT ? 472 : 512)) : ctx->cfg.top_nodes;
     if (topNodes > ctx->topNodesAvail) topNodes = ctx->topNodesAvail;
-    size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int);
+    size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int) + shareBytes;
     // keep MIN_BLOCKS CTAs resident inside the 227 KB a CTA can opt into
     const size_t smemBudget = (size_t)(227 * 1024) / MIN_BLOCKS - 1024;
     topNodes &= ~7;                                  // planes stay 128-byte aligned
@@ -305,6 +511,14 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     const long long needed = ((long long)p.numRays + BLOCK - 1) / BLOCK;
     if (grid > needed) grid = needed;
     if (grid < 1) grid = 1;
+    if (ANY_HIT) {
+        if (ctx->shareListCtas < (size_t)grid) {
+            if (ctx->shareList) { cudaFree(ctx->shareList); ctx->shareList = nullptr; ctx->shareListCtas = 0; }
+            B2RT_CUDA(ctx, cudaMalloc(&ctx->shareList, (size_t)grid * kShareList * sizeof(int)));
+            ctx->shareListCtas = (size_t)grid;
+        }
+        p.shareList = ctx->shareList;
+    }
     B2RT_CUDA(ctx, cudaMemsetAsync(p.warpCounter, 0, sizeof(int), stream));
     kern<<<(unsigned)grid, BLOCK, smem, stream>>>(p);
     B2RT_CHECK_LAUNCH(ctx, "traceKernel");
@@ -349,6 +563,8 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.nodesTex = ctx->nodesTex; p.woopTex = ctx->woopTex;
+    p.dummyLeaf = ~(int)(ctx->woopBytes / 16);       // first padding row: a terminator (api.cu:b2rt_set_bvh)
+    p.shareList = nullptr;
     if (flags & B2RT_TRACE_STATS) {
         B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
         B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev + 8, 0xff, 2 * sizeof(unsigned long long), stream));    // minima
@@ -359,6 +575,9 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // the tree wins on frame-sized batches (shorter tail, more node visits served from shared memory); four
         // 256-thread CTAs win on multi-million-ray batches
         variant = (numRays <= (4 << 20)) ? 6 : 1;
+        // any-hit batches share subtrees inside a CTA once the pool is dry; two 512-thread CTAs per SM measured best
+        // on C3's 2 Mi-ray AO batches (2 780 vs 2 710 Mrays/s for variant 6, 2 750 for variant 1)
+        if ((flags & B2RT_TRACE_ANY_HIT) && numRays <= (4 << 20)) variant = 7;
         // a BVH several times the size of L2 (126 MB): most node visits go to DRAM, and the 8-wide compressed private form
         // (80 bytes per 8 children instead of 64 per 2, trace_wide.cu) wins -- C4, 1.2 GB of Compact2 arrays: 500 vs 425
         // Mrays/s.  It is built on first use (host collapse of the private copy, api.cu:ensureWide).

@@ -76,6 +76,7 @@ typedef struct {
     /* the warp that left last: when it fetched its last rays, and the loop iterations it ran from then on --
      * the launch cannot end before that one bundle's dependent chain of node and triangle steps has */
     uint64_t ns_straggler_fetch, straggler_node_iters, straggler_tri_iters;
+    uint64_t shares;            /* any-hit kernels: stack entries handed to idle lanes after the pool ran dry */
 } b2rt_trace_stats;
 
 /* Tunables of the traversal kernel; zero-initialise and override what you need. */

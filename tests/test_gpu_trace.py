@@ -168,6 +168,60 @@ def test_wide_kernel_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     assert (got["id"][5::97] == -1).all() and (got["t"][5::97] == -1.0).all()
 
 
+@pytest.mark.parametrize("variant", [6, 1, 3])
+@pytest.mark.parametrize("kind,ntris", [("interior", 30000), ("knot", 40000)])
+@pytest.mark.parametrize("count", [1, 37, 4097, 0])
+def test_any_hit_subtree_sharing(b2rt, oracle, ctx, kind, ntris, variant, count):
+    """The any-hit kernels hand stack entries to idle lanes once the work counter is dry (trace.cu SHARE) and merge
+    the helpers' hits into the result record with an atomicMin; small batches run almost entirely in that mode.
+    Hit / no-hit must equal the oracle's for every ray, a reported hit must be a real one (t inside the ray's
+    interval, not in front of the closest hit), and with barycentrics on, u and v must be the values the plain
+    closest-hit kernel computes for the same triangle."""
+    scene = b2rt.Scene.generate(kind, ntris, 7)
+    bvh = b2rt.BVH(scene)
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.writeBarycentrics = True
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    origin, m = b2rt.camera_matrices(scene.camera, 128, 96)
+    rg = b2rt.RayGen(1 << 21, ctx)
+    prim = b2rt.RayBuffer()
+    rg.primary(prim, origin, m, 128, 96, scene.camera["far"])
+    tracer.traceBatch(prim)
+    sec = b2rt.RayBuffer()
+    rg.ao(sec, prim, scene, 4, 2.0 * float(np.linalg.norm(scene.verts.max(0) - scene.verts.min(0))) / 10.0, True)
+    rays = sec.getRays().copy()
+    if count:
+        rays = rays[np.linspace(0, len(rays) - 1, count).astype(np.int64)].copy()
+    rb = b2rt.RayBuffer(closestHit=False)
+    rb.setRays(rays)
+    rb.setNeedClosestHit(False)
+    try:
+        ctx.set_trace_config(variant=variant)
+        tracer.traceBatch(rb)
+        got = rb.getResults().copy()
+    finally:
+        ctx.set_trace_config()
+    ref = oracle.trace_woop(bvh.arrays(), rays, any_hit=False)          # closest hit: the strongest statement about hit / miss
+    agree = (got["id"] >= 0) == (ref["id"] >= 0)
+    assert agree.mean() >= (ID_AGREE if len(rays) > 10000 else 0.97), "hit/miss agreement %.6f" % agree.mean()
+    hit = (got["id"] >= 0) & (ref["id"] >= 0)
+    assert (got["t"][hit] > rays["tmin"][hit]).all() and (got["t"][hit] < rays["tmax"][hit]).all()
+    assert (got["t"][hit] >= ref["t"][hit] * (1 - 1e-5)).all()
+    miss = got["id"] < 0
+    assert (got["t"][miss] == rays["tmax"][miss]).all()
+    same = hit & (got["id"] == ref["id"])
+    if same.any():
+        rel = np.abs(got["t"][same] - ref["t"][same]) / np.abs(ref["t"][same])
+        assert rel.max() <= T_RTOL
+        # barycentrics of the merged record come from the fix-up pass: same bits as the closest-hit kernel's
+        rb.setNeedClosestHit(True)
+        tracer.traceBatch(rb)
+        closest = rb.getResults()
+        both = same & (closest["id"] == got["id"]) & (closest["t"] == got["t"])
+        assert both.sum() >= 0.9 * same.sum()
+        assert (closest["padA"][both] == got["padA"][both]).all() and (closest["padB"][both] == got["padB"][both]).all()
+
+
 def test_wide_kernel_any_hit_and_secondary(b2rt, oracle, ctx):
     scene = b2rt.Scene.generate("interior", 30000, 3)
     bvh = b2rt.BVH(scene)

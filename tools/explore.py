@@ -73,10 +73,10 @@ def main():
                                                                          100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"]))
                     continue
                 print("    stats: TRV %.1f%% IST %.1f%% fetches %d | warps %d pool empty %.1f us, warp exit mean %.1f p50 %.1f p90 %.1f p99 %.1f last %.1f us"
-                      " | last warp: last fetch at %.1f us, then %d node + %d triangle iterations" % (
+                      " | last warp: last fetch at %.1f us, then %d node + %d triangle iterations | shares %d" % (
                     100.0 * st["node_lanes"] / max(1, 32 * st["node_iters"]), 100.0 * st["tri_lanes"] / max(1, 32 * st["tri_iters"]), st["fetches"],
                     st["warps"], st["ns_pool_empty"] / 1e3, st["ns_mean_exit"] / 1e3, st["ns_exit_p50"] / 1e3, st["ns_exit_p90"] / 1e3,
-                    st["ns_exit_p99"] / 1e3, st["ns_last_exit"] / 1e3, st["ns_straggler_fetch"] / 1e3, st["straggler_node_iters"], st["straggler_tri_iters"]))
+                    st["ns_exit_p99"] / 1e3, st["ns_last_exit"] / 1e3, st["ns_straggler_fetch"] / 1e3, st["straggler_node_iters"], st["straggler_tri_iters"], st["shares"]))
             frame.tracer.collectStats = False
     ctx.set_trace_config()
     frame.trace_all()
