@@ -343,8 +343,10 @@ def product_arm(args):
     d2h = sum(hr.numel() * 4 for hr in host_res)
 
     def e2e_step():
+        # the frame's batches are independent host buffers: begin them all, wait once (b2rt_trace_host_begin / _end)
         for hr, hs, (rb, _) in zip(host_rays, host_res, frame.batches):
-            frame.tracer.traceHost(hr, hs, anyHit=not rb.getNeedClosestHit())
+            frame.tracer.traceHostBegin(hr, hs, anyHit=not rb.getNeedClosestHit())
+        frame.tracer.traceHostEnd()
 
     for _ in range(min(args.warmup, 3)):
         e2e_step()
@@ -414,7 +416,7 @@ def product_arm(args):
                    "bvh": "SBVH alpha 1e-5, Compact2, %d nodes, %d Woop rows" % (arrays["nodes"].size // 16, arrays["woop"].size // 4),
                    "parallelism": "BVH replicated, one frame per GPU" if not cfg.get("total_rays") else "BVH replicated, rays sharded"},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
-                "steps": e2e_steps, "ms_per_step": e2e_ms_max / e2e_steps, "api": "b2rt_trace_host (pinned host rays in, host hit records out)"},
+                "steps": e2e_steps, "ms_per_step": e2e_ms_max / e2e_steps, "api": "b2rt_trace_host_begin per batch + b2rt_trace_host_end per frame (pinned host rays in, host hit records out)"},
         "gpu_launches": int(launches_all),
         "wall_s_timed_region": t_wall,
         "clocks": sampler.summary(),

@@ -62,6 +62,8 @@ _SIGNATURES = {
     "b2rt_get_bvh": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]),
     "b2rt_trace": (i32, [vp, vp, vp, i64, C.c_uint, vp, C.POINTER(f32)]),
     "b2rt_trace_host": (i32, [vp, vp, vp, i64, C.c_uint, C.POINTER(f32), C.POINTER(f32)]),
+    "b2rt_trace_host_begin": (i32, [vp, vp, vp, i64, C.c_uint]),
+    "b2rt_trace_host_end": (i32, [vp, C.POINTER(f32), C.POINTER(f32)]),
     "b2rt_get_trace_stats": (i32, [vp, C.POINTER(TraceStats)]),
     "b2rt_count_work": (i32, [vp, vp, i64, i32, C.POINTER(WorkCounters), vp]),
     "b2rt_raygen_primary": (i32, [vp, vp, vp, i32, i32, f32, vp, vp, vp, vp, vp]),

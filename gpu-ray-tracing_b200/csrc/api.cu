@@ -32,12 +32,12 @@ int ensureScratch(b2rt_ctx* ctx, size_t bytes)
     return B2RT_OK;
 }
 
-static int ensureStage(b2rt_ctx* ctx, size_t bytes)
+static int ensureStage(b2rt_ctx* ctx, b2rt_ctx::HostSlot& slot, size_t bytes)
 {
-    if (bytes <= ctx->stageBytes) return B2RT_OK;
-    if (ctx->stage) { cudaFree(ctx->stage); ctx->stage = nullptr; ctx->stageBytes = 0; }
-    B2RT_CUDA(ctx, cudaMalloc(&ctx->stage, bytes));
-    ctx->stageBytes = bytes;
+    if (bytes <= slot.stageBytes) return B2RT_OK;
+    if (slot.stage) { cudaFree(slot.stage); slot.stage = nullptr; slot.stageBytes = 0; }
+    B2RT_CUDA(ctx, cudaMalloc(&slot.stage, bytes));
+    slot.stageBytes = bytes;
     return B2RT_OK;
 }
 
@@ -175,14 +175,17 @@ void b2rt_destroy(b2rt_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaFree(ctx->nodes); cudaFree(ctx->woop); cudaFree(ctx->triIndex);
     cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
-    cudaFree(ctx->shareList); cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch); cudaFree(ctx->stage);
+    cudaFree(ctx->shareList); cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch);
+    for (auto& slot : ctx->hostSlot) cudaFree(slot.stage);
     cudaFree(ctx->aabbDev); cudaFree(ctx->countDev);
     if (ctx->nodesTex) cudaDestroyTextureObject(ctx->nodesTex);
     if (ctx->woopTex) cudaDestroyTextureObject(ctx->woopTex);
     if (ctx->sIn) {
         cudaStreamDestroy(ctx->sIn); cudaStreamDestroy(ctx->sRun); cudaStreamDestroy(ctx->sOut);
-        for (int i = 0; i < b2rt_ctx::kHostChunks; i++) { cudaEventDestroy(ctx->evIn[i]); cudaEventDestroy(ctx->evK0[i]); cudaEventDestroy(ctx->evK1[i]); }
-        cudaEventDestroy(ctx->evT0); cudaEventDestroy(ctx->evT1);
+        for (auto& slot : ctx->hostSlot) {
+            for (int i = 0; i < b2rt_ctx::kHostChunks; i++) { cudaEventDestroy(slot.evIn[i]); cudaEventDestroy(slot.evK0[i]); cudaEventDestroy(slot.evK1[i]); }
+            cudaEventDestroy(slot.evT0); cudaEventDestroy(slot.evT1);
+        }
     }
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -299,73 +302,116 @@ int b2rt_trace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, 
     return B2RT_OK;
 }
 
+// Wait for one in-flight host batch and add its times to the running totals.
+static int finishHostSlot(b2rt_ctx* ctx, b2rt_ctx::HostSlot& slot, float* msKernel, cudaEvent_t* first, cudaEvent_t* last)
+{
+    if (!slot.inFlight) return B2RT_OK;
+    slot.inFlight = false;
+    B2RT_CUDA(ctx, cudaEventSynchronize(slot.evT1));
+    if (msKernel)
+        for (int c = 0; c < slot.chunks; c++) { float t = 0.0f; cudaEventElapsedTime(&t, slot.evK0[c], slot.evK1[c]); *msKernel += t; }
+    if (first && !*first) *first = slot.evT0;
+    if (last) *last = slot.evT1;
+    return B2RT_OK;
+}
+
+int b2rt_trace_host_begin(b2rt_ctx* ctx, const void* raysHost, void* resultsHost, int64_t numRays, unsigned flags)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (numRays == 0) return B2RT_OK;
+    if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
+    if (numRays < 0 || numRays > 0x7fffffff || !raysHost || !resultsHost)
+        return setError(ctx, B2RT_ERR_ARG, "b2rt_trace_host: bad ray buffer (n=%lld)", (long long)numRays);
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    // Three streams, up to kHostChunks chunks per batch: the upload of chunk i+1, the trace of chunk i and the download of
+    // chunk i-1 overlap (PCIe is full duplex), so a batch costs about max(upload, download) instead of their sum + the
+    // kernel; with a second batch begun before the first is waited for, its upload also hides the first one's last
+    // kernel and download.
+    if (!ctx->sIn) {
+        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sIn, cudaStreamNonBlocking));
+        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sRun, cudaStreamNonBlocking));
+        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sOut, cudaStreamNonBlocking));
+        for (auto& slot : ctx->hostSlot) {
+            for (int i = 0; i < b2rt_ctx::kHostChunks; i++) {
+                B2RT_CUDA(ctx, cudaEventCreateWithFlags(&slot.evIn[i], cudaEventDisableTiming));
+                B2RT_CUDA(ctx, cudaEventCreate(&slot.evK0[i]));
+                B2RT_CUDA(ctx, cudaEventCreate(&slot.evK1[i]));
+            }
+            B2RT_CUDA(ctx, cudaEventCreate(&slot.evT0));
+            B2RT_CUDA(ctx, cudaEventCreate(&slot.evT1));
+        }
+    }
+    b2rt_ctx::HostSlot& slot = ctx->hostSlot[ctx->nextHostSlot];
+    ctx->nextHostSlot = (ctx->nextHostSlot + 1) % b2rt_ctx::kHostSlots;
+    int rc = finishHostSlot(ctx, slot, nullptr, nullptr, nullptr);       // both slots busy: the older batch has to drain first
+    if (rc) return rc;
+    const size_t rayBytes = (size_t)numRays * sizeof(Ray), resBytes = (size_t)numRays * sizeof(RayResult);
+    rc = ensureStage(ctx, slot, rayBytes + resBytes);
+    if (rc) return rc;
+    // 256 Ki rays per chunk: measured best on C2 (64 Ki 876, 128 Ki 1 055, 192 Ki 1 225, 256 Ki 1 275, 400 K 1 138 Mrays/s
+    // end to end) -- smaller chunks make the launches tail-bound and slower than their own upload
+    int chunks = (int)std::min<int64_t>(b2rt_ctx::kHostChunks, std::max<int64_t>(1, numRays / (256 * 1024)));
+    const int64_t per = ((numRays + chunks - 1) / chunks + 31) & ~int64_t(31);
+    chunks = (int)((numRays + per - 1) / per);
+    char* dRays = static_cast<char*>(slot.stage);
+    char* dRes = dRays + rayBytes;
+    const char* hRays = static_cast<const char*>(raysHost);
+    char* hRes = static_cast<char*>(resultsHost);
+    const bool clearPads = !(flags & (B2RT_TRACE_WRITE_BARY | B2RT_TRACE_STATS));
+    cudaError_t e = cudaEventRecord(slot.evT0, ctx->sIn);
+    for (int c = 0; c < chunks && e == cudaSuccess && rc == 0; c++) {
+        const int64_t lo = c * per, n = std::min<int64_t>(per, numRays - lo);
+        e = cudaMemcpyAsync(dRays + lo * sizeof(Ray), hRays + lo * sizeof(Ray), (size_t)n * sizeof(Ray), cudaMemcpyHostToDevice, ctx->sIn);
+        if (e == cudaSuccess) e = cudaEventRecord(slot.evIn[c], ctx->sIn);
+        // the kernel writes only id and t without WRITE_BARY (as CudaTracerKernels.hh:197): the pad words that
+        // travel back to the host are zero, not stale staging memory
+        if (e == cudaSuccess && clearPads) e = cudaMemsetAsync(dRes + lo * sizeof(RayResult), 0, (size_t)n * sizeof(RayResult), ctx->sRun);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->sRun, slot.evIn[c], 0);
+        if (e == cudaSuccess) e = cudaEventRecord(slot.evK0[c], ctx->sRun);
+        if (e == cudaSuccess) rc = launchTrace(ctx, dRays + lo * sizeof(Ray), dRes + lo * sizeof(RayResult), n, flags, ctx->sRun);
+        if (e == cudaSuccess && rc == 0) e = cudaEventRecord(slot.evK1[c], ctx->sRun);
+        if (e == cudaSuccess && rc == 0) e = cudaStreamWaitEvent(ctx->sOut, slot.evK1[c], 0);
+        if (e == cudaSuccess && rc == 0)
+            e = cudaMemcpyAsync(hRes + lo * sizeof(RayResult), dRes + lo * sizeof(RayResult), (size_t)n * sizeof(RayResult), cudaMemcpyDeviceToHost, ctx->sOut);
+    }
+    if (e == cudaSuccess && rc == 0) e = cudaEventRecord(slot.evT1, ctx->sOut);
+    if (rc || e != cudaSuccess) {
+        cudaStreamSynchronize(ctx->sOut); cudaStreamSynchronize(ctx->sRun); cudaStreamSynchronize(ctx->sIn);
+        if (rc) return rc;
+        return setError(ctx, B2RT_ERR_CUDA, "b2rt_trace_host: %s", cudaGetErrorString(e));
+    }
+    slot.chunks = chunks;
+    slot.inFlight = true;
+    return B2RT_OK;
+}
+
+int b2rt_trace_host_end(b2rt_ctx* ctx, float* msKernel, float* msTotal)
+{
+    if (!ctx) return B2RT_ERR_ARG;
+    if (msKernel) *msKernel = 0.0f;
+    if (msTotal) *msTotal = 0.0f;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaEvent_t first = nullptr, last = nullptr;
+    // oldest first: nextHostSlot is the slot the next begin would take, i.e. the older of the two
+    for (int k = 0; k < b2rt_ctx::kHostSlots; k++) {
+        const int rc = finishHostSlot(ctx, ctx->hostSlot[(ctx->nextHostSlot + k) % b2rt_ctx::kHostSlots], msKernel, &first, &last);
+        if (rc) return rc;
+    }
+    if (msTotal && first && last) cudaEventElapsedTime(msTotal, first, last);
+    return B2RT_OK;
+}
+
 int b2rt_trace_host(b2rt_ctx* ctx, const void* raysHost, void* resultsHost, int64_t numRays, unsigned flags,
                     float* msKernel, float* msTotal)
 {
     if (!ctx) return B2RT_ERR_ARG;
     if (msKernel) *msKernel = 0.0f;
     if (msTotal) *msTotal = 0.0f;
-    if (numRays == 0) return B2RT_OK;
-    if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
-    if (numRays < 0 || numRays > 0x7fffffff || !raysHost || !resultsHost)
-        return setError(ctx, B2RT_ERR_ARG, "b2rt_trace_host: bad ray buffer (n=%lld)", (long long)numRays);
-    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
-    const size_t rayBytes = (size_t)numRays * sizeof(Ray), resBytes = (size_t)numRays * sizeof(RayResult);
-    int rc = ensureStage(ctx, rayBytes + resBytes);
+    int rc = b2rt_trace_host_end(ctx, nullptr, nullptr);         // batches begun earlier are not part of this call's times
     if (rc) return rc;
-    // Three streams, up to kHostChunks chunks: the upload of chunk i+1, the trace of chunk i and the download of chunk
-    // i-1 overlap (PCIe is full duplex), so the call costs about max(upload, download) instead of their sum + the kernel.
-    if (!ctx->sIn) {
-        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sIn, cudaStreamNonBlocking));
-        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sRun, cudaStreamNonBlocking));
-        B2RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sOut, cudaStreamNonBlocking));
-        for (int i = 0; i < b2rt_ctx::kHostChunks; i++) {
-            B2RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->evIn[i], cudaEventDisableTiming));
-            B2RT_CUDA(ctx, cudaEventCreate(&ctx->evK0[i]));
-            B2RT_CUDA(ctx, cudaEventCreate(&ctx->evK1[i]));
-        }
-        B2RT_CUDA(ctx, cudaEventCreate(&ctx->evT0));
-        B2RT_CUDA(ctx, cudaEventCreate(&ctx->evT1));
-    }
-    int chunks = (int)std::min<int64_t>(b2rt_ctx::kHostChunks, std::max<int64_t>(1, numRays / (256 * 1024)));
-    const int64_t per = ((numRays + chunks - 1) / chunks + 31) & ~int64_t(31);
-    chunks = (int)((numRays + per - 1) / per);
-    char* dRays = static_cast<char*>(ctx->stage);
-    char* dRes = dRays + rayBytes;
-    const char* hRays = static_cast<const char*>(raysHost);
-    char* hRes = static_cast<char*>(resultsHost);
-    const bool clearPads = !(flags & (B2RT_TRACE_WRITE_BARY | B2RT_TRACE_STATS));
-    cudaError_t e = cudaEventRecord(ctx->evT0, ctx->sIn);
-    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->sOut, ctx->evT0, 0);      // total time starts with the first upload
-    for (int c = 0; c < chunks && e == cudaSuccess && rc == 0; c++) {
-        const int64_t lo = c * per, n = std::min<int64_t>(per, numRays - lo);
-        e = cudaMemcpyAsync(dRays + lo * sizeof(Ray), hRays + lo * sizeof(Ray), (size_t)n * sizeof(Ray), cudaMemcpyHostToDevice, ctx->sIn);
-        if (e == cudaSuccess) e = cudaEventRecord(ctx->evIn[c], ctx->sIn);
-        // the kernel writes only id and t without WRITE_BARY (as CudaTracerKernels.hh:197): the pad words that
-        // travel back to the host are zero, not stale staging memory
-        if (e == cudaSuccess && clearPads) e = cudaMemsetAsync(dRes + lo * sizeof(RayResult), 0, (size_t)n * sizeof(RayResult), ctx->sRun);
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->sRun, ctx->evIn[c], 0);
-        if (e == cudaSuccess) e = cudaEventRecord(ctx->evK0[c], ctx->sRun);
-        if (e == cudaSuccess) rc = launchTrace(ctx, dRays + lo * sizeof(Ray), dRes + lo * sizeof(RayResult), n, flags, ctx->sRun);
-        if (e == cudaSuccess && rc == 0) e = cudaEventRecord(ctx->evK1[c], ctx->sRun);
-        if (e == cudaSuccess && rc == 0) e = cudaStreamWaitEvent(ctx->sOut, ctx->evK1[c], 0);
-        if (e == cudaSuccess && rc == 0)
-            e = cudaMemcpyAsync(hRes + lo * sizeof(RayResult), dRes + lo * sizeof(RayResult), (size_t)n * sizeof(RayResult), cudaMemcpyDeviceToHost, ctx->sOut);
-    }
-    if (e == cudaSuccess && rc == 0) e = cudaEventRecord(ctx->evT1, ctx->sOut);
-    cudaError_t es = cudaStreamSynchronize(ctx->sOut);
-    cudaStreamSynchronize(ctx->sRun);
-    cudaStreamSynchronize(ctx->sIn);
-    if (e == cudaSuccess) e = es;
+    rc = b2rt_trace_host_begin(ctx, raysHost, resultsHost, numRays, flags);
     if (rc) return rc;
-    if (e != cudaSuccess) return setError(ctx, B2RT_ERR_CUDA, "b2rt_trace_host: %s", cudaGetErrorString(e));
-    if (msKernel) {
-        float sum = 0.0f;
-        for (int c = 0; c < chunks; c++) { float t = 0.0f; cudaEventElapsedTime(&t, ctx->evK0[c], ctx->evK1[c]); sum += t; }
-        *msKernel = sum;
-    }
-    if (msTotal) cudaEventElapsedTime(msTotal, ctx->evT0, ctx->evT1);
-    return B2RT_OK;
+    return b2rt_trace_host_end(ctx, msKernel, msTotal);
 }
 
 int b2rt_count_work(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, void* stream)

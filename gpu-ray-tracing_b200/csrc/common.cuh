@@ -56,12 +56,18 @@ struct b2rt_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // b2rt_trace_host: upload / trace / download pipeline
     static constexpr int kHostChunks = 8;
+    static constexpr int kHostSlots = 2;        // host batches in flight (b2rt_trace_host_begin / _end)
     cudaStream_t sIn = nullptr, sRun = nullptr, sOut = nullptr;
-    cudaEvent_t evIn[kHostChunks] = {}, evK0[kHostChunks] = {}, evK1[kHostChunks] = {}, evT0 = nullptr, evT1 = nullptr;
+    struct HostSlot {
+        cudaEvent_t evIn[kHostChunks] = {}, evK0[kHostChunks] = {}, evK1[kHostChunks] = {}, evT0 = nullptr, evT1 = nullptr;
+        void* stage = nullptr; size_t stageBytes = 0;       // device staging: rays, then results
+        int chunks = 0;
+        bool inFlight = false;
+    } hostSlot[kHostSlots];
+    int nextHostSlot = 0;
 
     // scratch (grown on demand, never shrunk)
     void* scratch = nullptr;  size_t scratchBytes = 0;
-    void* stage = nullptr;    size_t stageBytes = 0;   // device staging for b2rt_trace_host
     int* shareList = nullptr; size_t shareListCtas = 0; // any-hit kernels: shared-ray lists, one slice per CTA (trace.cu)
     float* aabbDev = nullptr;                   // 6 floats
     long long* countDev = nullptr;              // hit counter

@@ -516,6 +516,19 @@ class CudaTracer:
                                     n, flags, C.byref(k), C.byref(t)), self._ctx.handle)
         return k.value, t.value
 
+    def traceHostBegin(self, rays_host, results_host, anyHit=False):
+        """First half of traceHost: enqueue upload, trace and download of one host batch and return (up to two batches in
+        flight; b2rt_trace_host_begin).  The tensors must stay alive and unread until traceHostEnd."""
+        flags = (TRACE_ANY_HIT if anyHit else 0) | (TRACE_WRITE_BARY if self.writeBarycentrics else 0)
+        check(lib().b2rt_trace_host_begin(self._ctx.handle, C.c_void_p(rays_host.data_ptr()), C.c_void_p(results_host.data_ptr()),
+                                          rays_host.shape[0], flags), self._ctx.handle)
+
+    def traceHostEnd(self):
+        """Wait for every batch begun; returns (summed kernel_ms, device ms from the first upload to the last download)."""
+        k, t = C.c_float(), C.c_float()
+        check(lib().b2rt_trace_host_end(self._ctx.handle, C.byref(k), C.byref(t)), self._ctx.handle)
+        return k.value, t.value
+
     def countWork(self, rays):
         """Canonical per-batch work counters (b2rt_count_work): N_n, N_t, N_l, N_u, N_v, hits."""
         w = _lib.WorkCounters()

@@ -123,6 +123,13 @@ int b2rt_trace(b2rt_ctx* ctx, const void* rays_dev, void* results_dev, int64_t n
  * rays, trace, D2H copy of the results, all inside the call.  ms_kernel / ms_total optional. */
 int b2rt_trace_host(b2rt_ctx* ctx, const void* rays_host, void* results_host, int64_t num_rays,
                     unsigned flags, float* ms_kernel, float* ms_total);
+/* The same in two halves, for callers with several independent batches (a frame's batches, CudaTracer.cc:119-178 called
+ * in a loop by Renderer.cc:262-330): _begin enqueues upload, trace and download and returns; up to two batches may be
+ * in flight (a third _begin first waits for the oldest), so the second batch's upload overlaps the first one's last
+ * kernel and download.  _end waits for everything begun and returns the summed kernel time and the device time from
+ * the first upload to the last download.  The host buffers must stay valid, and the results unread, until _end. */
+int b2rt_trace_host_begin(b2rt_ctx* ctx, const void* rays_host, void* results_host, int64_t num_rays, unsigned flags);
+int b2rt_trace_host_end(b2rt_ctx* ctx, float* ms_kernel, float* ms_total);
 /* counters of the last B2RT_TRACE_STATS launch (synchronises) */
 int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out);
 

@@ -247,3 +247,65 @@ def test_wide_kernel_any_hit_and_secondary(b2rt, oracle, ctx):
         _check_closest(oracle, bvh.arrays(), rays, sec.getResults(), ref)
     finally:
         ctx.set_trace_config()
+
+
+def _host_batches(b2rt, oracle, ctx, scene, tracer, sizes):
+    """Primary-ray batches of the given pixel sizes, as (device RayBuffer traced on the device, pinned host rays)."""
+    import torch
+    out = []
+    for (w, h) in sizes:
+        rays = _primary_rays(b2rt, oracle, scene, w, h)
+        rb = b2rt.RayBuffer()
+        rb.setRays(rays)
+        tracer.traceBatch(rb)
+        hr = torch.from_numpy(rays.view(np.float32).reshape(-1, 8).copy()).pin_memory()
+        out.append((rb, hr))
+    return out
+
+
+def test_trace_host_matches_device_path(b2rt, oracle, ctx):
+    """b2rt_trace_host (host rays in, host hit records out; chunked upload / trace / download pipeline) returns the
+    records b2rt_trace leaves on the device, pads zeroed; pageable buffers work too; an empty batch is a no-op."""
+    import torch
+    scene = b2rt.Scene.generate("interior", 30000, 5)
+    bvh = b2rt.BVH(scene)
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    (rb, hr), = _host_batches(b2rt, oracle, ctx, scene, tracer, [(1024, 600)])      # 614 400 rays: two chunks
+    dev = rb.getResults()
+    for pinned in (True, False):
+        rays_h = hr if pinned else hr.clone()
+        res_h = torch.full((hr.shape[0], 4), 7, dtype=torch.int32)
+        if pinned:
+            res_h = res_h.pin_memory()
+        k, t = tracer.traceHost(rays_h, res_h)
+        assert 0.0 < k <= t
+        got = res_h.numpy().view(oracle.RESULT_DTYPE).reshape(-1)
+        assert (got["id"] == dev["id"]).mean() >= ID_AGREE
+        same = got["id"] == dev["id"]
+        assert (got["t"][same] == dev["t"][same]).all()
+        assert (got["padA"] == 0).all() and (got["padB"] == 0).all()
+    k, t = tracer.traceHost(hr[:0], torch.empty((0, 4), dtype=torch.int32))
+    assert k == 0.0 and t == 0.0
+
+
+def test_trace_host_begin_end_keeps_batches_apart(b2rt, oracle, ctx):
+    """Three batches begun back to back (the third has to wait for the first slot), one wait: every batch gets its own
+    records, identical to the device path's."""
+    import torch
+    scene = b2rt.Scene.generate("knot", 40000, 5)
+    bvh = b2rt.BVH(scene)
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    batches = _host_batches(b2rt, oracle, ctx, scene, tracer, [(640, 480), (203, 77), (800, 700)])
+    outs = [torch.full((hr.shape[0], 4), -5, dtype=torch.int32).pin_memory() for _, hr in batches]
+    for (rb, hr), res_h in zip(batches, outs):
+        tracer.traceHostBegin(hr, res_h)
+    k, t = tracer.traceHostEnd()
+    assert 0.0 < k <= t
+    for (rb, hr), res_h in zip(batches, outs):
+        dev = rb.getResults()
+        got = res_h.numpy().view(oracle.RESULT_DTYPE).reshape(-1)
+        same = got["id"] == dev["id"]
+        assert same.mean() >= ID_AGREE and (got["t"][same] == dev["t"][same]).all()
+    assert tracer.traceHostEnd() == (0.0, 0.0)          # nothing in flight
