@@ -404,6 +404,10 @@ def product_arm(args):
             traffic = json.load(f).get(name, {}).get("dram_bytes_per_launch")
     except Exception:
         pass
+    # the other reading of "algorithmic": bytes that HAVE to cross the HBM interface -- every ray in, every hit record out,
+    # the BVH arrays once per step (L2 is flushed between steps) -- against the ncu-measured DRAM traffic of the launch
+    bvh_bytes = float(arrays["nodes"].nbytes + arrays["woop"].nbytes + arrays["triIndex"].nbytes)
+    compulsory = (launched / n_launch_step) * (32 + 8) + bvh_bytes / n_launch_step
     sm_hz = (sampler.summary()["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)) * 1e6
     sm_count = ctx.sm_count()
     fp32_rate = fp32_all / ws / (ms_total_max / args.steps * 1e-3)
@@ -423,6 +427,9 @@ def product_arm(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                      "traffic": traffic, "peak_source": peak_src, "kernel": "traceKernel",
                      "algorithmic_bytes_per_launch": bytes_all / ws / n_launch_step, "avg_launch_ms": avg_launch_ms,
+                     "compulsory": {"bytes_per_launch": compulsory, "achieved": compulsory / (avg_launch_ms * 1e-3) * 1e-9,
+                                    "frac": compulsory / (avg_launch_ms * 1e-3) * 1e-9 / peak_gbs,
+                                    "traffic_over_compulsory": (traffic / compulsory) if traffic else None},
                      "note": "algorithmic bytes count every node/triangle fetch (SURVEY 8d); the BVH is L2/L1 resident, so frac > 1 is "
                              "expected and DRAM traffic is far below it -- the binding ceiling is instruction issue, see issue_roofline"},
         "issue_roofline": {"fp32_inst_per_s": fp32_rate, "fp32_peak_inst_per_s": sm_count * 128 * sm_hz,

@@ -103,11 +103,11 @@ class Frame:
         total = c.get("total_rays")
         if total:
             # C5: ONE buffer of `total` diffuse rays (primaries x samples).  Sharded over ranks in interleaved chunks of
-            # 1024 primaries (contiguous slices of an image-ordered buffer have unequal cost -- sky vs
+            # 64 primaries = one 8x8 pixel block (contiguous slices of an image-ordered buffer have unequal cost -- sky vs
             # geometry -- so each rank takes every ws-th chunk); the last rank's slice is cut so the total is exact.
             n_prim_needed = (total + samples - 1) // samples
             big = RayGen(1 << 30, self.ctx)
-            chunk = 1024
+            chunk = 64
             idx = torch.arange(n_prim_needed, device=self.device)
             mine = idx[((idx // chunk) % ws) == rank]
             sub = _gather_buffer(self.primary, mine)
