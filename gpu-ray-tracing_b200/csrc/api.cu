@@ -155,7 +155,7 @@ int b2rt_create(int device, b2rt_ctx** out)
     ctx->l2Bytes = (size_t)prop.l2CacheSize;
     ctx->ccMajor = prop.major; ctx->ccMinor = prop.minor;
     if ((e = cudaSetDevice(device)) != cudaSuccess ||
-        (e = cudaMalloc(&ctx->warpCounter, 64)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->warpCounter, b2rt_ctx::kLaunchSlots * 128)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->statsDev, (16 + 3 * kTimelineWarps) * sizeof(unsigned long long))) != cudaSuccess ||
         (e = cudaMalloc(&ctx->aabbDev, 8 * sizeof(float))) != cudaSuccess ||
         (e = cudaMalloc(&ctx->countDev, sizeof(long long))) != cudaSuccess ||

@@ -51,7 +51,11 @@ struct b2rt_ctx {
 
     b2rt_trace_config cfg = { -1, -1, -1, -1, -1 };
 
-    int* warpCounter = nullptr;                 // work counter for persistent warps
+    // Launch slots: every trace launch takes the next of kLaunchSlots work counters (and, for the any-hit kernels, the
+    // next slice of the shared-ray lists), so traces issued on different streams may overlap -- up to kLaunchSlots in flight.
+    static constexpr int kLaunchSlots = 8;
+    int* warpCounter = nullptr;                 // kLaunchSlots work counters for persistent warps, 128 bytes apart
+    unsigned launchSlot = 0;
     unsigned long long* statsDev = nullptr;     // 16 counters for the instrumented kernel + kTimelineWarps exit times
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // b2rt_trace_host: upload / trace / download pipeline

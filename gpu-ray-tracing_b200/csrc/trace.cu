@@ -65,7 +65,7 @@ struct ShareArea {
 constexpr int kShareSteps = 4;      // tail of the launch: node steps between two visits of the queue
 constexpr int kShareRounds = 4;     // stack entries a lane may hand over per visit
 constexpr int kShareQueue = 128;    // queue entries (int4: ray, stack entry, hit distance); 2 KB keeps the L1 carve-out where it was
-constexpr int kShareList = 4096;    // shared rays per CTA (global memory)
+constexpr int kShareList = 1024;    // shared rays per CTA (global memory, one slice per CTA and launch slot)
 
 template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
@@ -511,13 +511,15 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     const long long needed = ((long long)p.numRays + BLOCK - 1) / BLOCK;
     if (grid > needed) grid = needed;
     if (grid < 1) grid = 1;
+    const unsigned slot = ctx->launchSlot++ % b2rt_ctx::kLaunchSlots;
+    p.warpCounter = ctx->warpCounter + slot * 32;
     if (ANY_HIT) {
         if (ctx->shareListCtas < (size_t)grid) {
             if (ctx->shareList) { cudaFree(ctx->shareList); ctx->shareList = nullptr; ctx->shareListCtas = 0; }
-            B2RT_CUDA(ctx, cudaMalloc(&ctx->shareList, (size_t)grid * kShareList * sizeof(int)));
+            B2RT_CUDA(ctx, cudaMalloc(&ctx->shareList, (size_t)b2rt_ctx::kLaunchSlots * grid * kShareList * sizeof(int)));
             ctx->shareListCtas = (size_t)grid;
         }
-        p.shareList = ctx->shareList;
+        p.shareList = ctx->shareList + (size_t)slot * ctx->shareListCtas * kShareList;
     }
     B2RT_CUDA(ctx, cudaMemsetAsync(p.warpCounter, 0, sizeof(int), stream));
     kern<<<(unsigned)grid, BLOCK, smem, stream>>>(p);

@@ -244,6 +244,7 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     const long long needed = ((long long)p.numRays + BLOCK - 1) / BLOCK;
     if (grid > needed) grid = needed;
     if (grid < 1) grid = 1;
+    p.warpCounter = ctx->warpCounter + (ctx->launchSlot++ % b2rt_ctx::kLaunchSlots) * 32;
     B2RT_CUDA(ctx, cudaMemsetAsync(p.warpCounter, 0, sizeof(int), stream));
     kern<<<(unsigned)grid, BLOCK, 0, stream>>>(p);
     B2RT_CHECK_LAUNCH(ctx, "traceWideKernel");

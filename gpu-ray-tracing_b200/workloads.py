@@ -143,6 +143,34 @@ class Frame:
         """Trace every batch once; returns the summed kernel milliseconds (App.cc:194-204)."""
         return sum(self.tracer.traceBatch(rb) for rb, _ in self.batches)
 
+    def trace_all_overlapped(self, n_streams=2):
+        """The frame's batches issued round-robin on `n_streams` streams without waiting in between: batches that do not
+        depend on each other (the secondary batches of a frame all depend on the primary batch only) may overlap, so the
+        idle tail of one launch is filled by the next.  Returns the device milliseconds from the first launch's start to
+        the last one's end.  The primary batch, when it is part of the frame, is traced first and waited for."""
+        if not hasattr(self, "_streams") or len(self._streams) != n_streams:
+            self._streams = [torch.cuda.Stream(device=self.device) for _ in range(n_streams)]
+        cur = torch.cuda.current_stream(self.device)
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        start.record(cur)
+        batches = list(self.batches)
+        if batches and batches[0][0] is self.primary:
+            self.tracer.traceBatchAsync(self.primary)           # on the current stream; the others wait for `ready`
+            batches = batches[1:]
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        for k, (rb, _) in enumerate(batches):
+            s = self._streams[k % n_streams]
+            if k < n_streams:
+                s.wait_event(ready)
+            with torch.cuda.stream(s):
+                self.tracer.traceBatchAsync(rb)
+        for s in self._streams:
+            cur.wait_stream(s)
+        end.record(cur)
+        end.synchronize()
+        return start.elapsed_time(end)
+
 
 def _gather_buffer(rb, index):
     """RayBuffer holding the rays and results of the given slots (identity id maps)."""

@@ -116,7 +116,10 @@ int b2rt_get_bvh(const b2rt_ctx* ctx, const void** nodes_dev, size_t* node_bytes
 /* replaces CudaTracer::traceBatch + launch_tracingKernel (CudaTracer.cc:119-178,
  * kepler_dynamic_fetch.cu:432-474).  If ms != NULL the launch is bracketed by CUDA events on
  * `stream`, the call synchronises and *ms receives the kernel time in milliseconds (what the
- * reference returns); if ms == NULL the call is asynchronous.  num_rays == 0 returns 0 ms. */
+ * reference returns); if ms == NULL the call is asynchronous.  num_rays == 0 returns 0 ms.
+ * Asynchronous traces issued on DIFFERENT streams may overlap (the reference allows one trace in flight per device:
+ * one g_warpCounter, kepler_dynamic_fetch.cu:58): up to 8 may be in flight per context, so the idle tail of one batch
+ * can be filled by the next independent one.  B2RT_TRACE_STATS launches are not safe to overlap. */
 int b2rt_trace(b2rt_ctx* ctx, const void* rays_dev, void* results_dev, int64_t num_rays,
                unsigned flags, void* stream, float* ms);
 /* end-to-end variant for callers holding HOST buffers (pinned or pageable): H2D copy of the

@@ -309,3 +309,40 @@ def test_trace_host_begin_end_keeps_batches_apart(b2rt, oracle, ctx):
         same = got["id"] == dev["id"]
         assert same.mean() >= ID_AGREE and (got["t"][same] == dev["t"][same]).all()
     assert tracer.traceHostEnd() == (0.0, 0.0)          # nothing in flight
+
+
+def test_traces_on_two_streams_overlap_safely(b2rt, oracle, ctx):
+    """Launch slots (one work counter and one shared-ray list slice per launch): asynchronous traces issued on different
+    streams give each batch the records the synchronous path gives it -- closest-hit and any-hit, several rounds."""
+    import torch
+    scene = b2rt.Scene.generate("knot", 40000, 9)
+    bvh = b2rt.BVH(scene)
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    origin, m = b2rt.camera_matrices(scene.camera, 320, 240)
+    rg = b2rt.RayGen(1 << 21, ctx)
+    prim = b2rt.RayBuffer()
+    rg.primary(prim, origin, m, 320, 240, scene.camera["far"])
+    tracer.traceBatch(prim)
+    batches = []
+    for samples, closest in ((4, True), (8, False), (2, True), (16, False), (1, True), (6, False)):
+        sec = b2rt.RayBuffer()
+        rg.ao(sec, prim, scene, samples, 3.0, True)
+        sec.setNeedClosestHit(closest)
+        tracer.traceBatch(sec)
+        batches.append((sec, sec.getResults().copy()))
+    streams = [torch.cuda.Stream() for _ in range(3)]
+    for _ in range(5):
+        for rb, _ in batches:
+            rb.m_results.fill_(-7)
+        torch.cuda.synchronize()
+        for k, (rb, _) in enumerate(batches):
+            with torch.cuda.stream(streams[k % 3]):
+                tracer.traceBatchAsync(rb)
+        torch.cuda.synchronize()
+        for rb, want in batches:
+            got = rb.getResults()
+            assert ((got["id"] >= 0) == (want["id"] >= 0)).all()
+            if rb.getNeedClosestHit():
+                same = got["id"] == want["id"]
+                assert same.mean() >= 0.999 and (got["t"][same] == want["t"][same]).all()

@@ -52,14 +52,16 @@ def main():
     sweeps = configs or ["v1", "v6", "v7", "v100", "v101", "v102", "v103"]
     for s in sweeps:
         kw = {}
+        overlap = 0
         for tok in s.split(","):
             if tok.startswith("v"): kw["variant"] = int(tok[1:])
             if tok.startswith("t"): kw["top_nodes"] = int(tok[1:])
             if tok.startswith("f"): kw["fetch_threshold"] = int(tok[1:])
             if tok.startswith("b"): kw["blocks_per_sm"] = int(tok[1:])
             if tok.startswith("p"): kw["l2_prefetch"] = int(tok[1:])
+            if tok.startswith("o"): overlap = int(tok[1:])
         ctx.set_trace_config(**kw)
-        ms = median_ms(frame.trace_all)
+        ms = median_ms((lambda: frame.trace_all_overlapped(overlap)) if overlap else frame.trace_all)
         out[s] = counted / ms / 1e3
         print("%-16s %8.3f ms  %9.1f Mrays/s" % (s, ms, out[s]), flush=True)
         if kw.get("variant", 0) < 100:
