@@ -158,7 +158,9 @@ int b2rt_create(int device, b2rt_ctx** out)
         (e = cudaMalloc(&ctx->warpCounter, b2rt_ctx::kLaunchSlots * 128)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->statsDev, (16 + 3 * kTimelineWarps) * sizeof(unsigned long long))) != cudaSuccess ||
         (e = cudaMalloc(&ctx->aabbDev, 8 * sizeof(float))) != cudaSuccess ||
-        (e = cudaMalloc(&ctx->countDev, sizeof(long long))) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->countDev, 2 * sizeof(long long))) != cudaSuccess ||
+        (e = cudaMemset(ctx->countDev, 0, 2 * sizeof(long long))) != cudaSuccess ||
+        (e = cudaHostAlloc(&ctx->countHost, sizeof(long long), cudaHostAllocMapped | cudaHostAllocPortable)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
         setError(nullptr, B2RT_ERR_CUDA, "b2rt_create: %s", cudaGetErrorString(e));
         b2rt_destroy(ctx);
@@ -177,7 +179,7 @@ void b2rt_destroy(b2rt_ctx* ctx)
     cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
     cudaFree(ctx->shareList); cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch);
     for (auto& slot : ctx->hostSlot) cudaFree(slot.stage);
-    cudaFree(ctx->aabbDev); cudaFree(ctx->countDev);
+    cudaFree(ctx->aabbDev); cudaFree(ctx->countDev); cudaFreeHost(ctx->countHost);
     if (ctx->nodesTex) cudaDestroyTextureObject(ctx->nodesTex);
     if (ctx->woopTex) cudaDestroyTextureObject(ctx->woopTex);
     if (ctx->sIn) {

@@ -74,7 +74,8 @@ struct b2rt_ctx {
     void* scratch = nullptr;  size_t scratchBytes = 0;
     int* shareList = nullptr; size_t shareListCtas = 0; // any-hit kernels: shared-ray lists, one slice per CTA (trace.cu)
     float* aabbDev = nullptr;                   // 6 floats
-    long long* countDev = nullptr;              // hit counter
+    long long* countDev = nullptr;              // hit counter: running sum + finished-block count (misc.cu)
+    long long* countHost = nullptr;             // mapped pinned word the last block writes the total to
 };
 
 namespace b2rt {

@@ -6,7 +6,10 @@
 
 namespace b2rt {
 
-__global__ void __launch_bounds__(256) countHitsKernel(const int4* __restrict__ results, long long n, unsigned long long* out)
+// state[0] = running sum, state[1] = finished blocks.  The last block to finish hands the total to the host through a
+// mapped pinned word and leaves both words zero for the next call: no memset before and no copy after the launch.
+__global__ void __launch_bounds__(256) countHitsKernel(const int4* __restrict__ results, long long n,
+                                                       unsigned long long* state, unsigned long long* hostOut)
 {
     unsigned c = 0;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
@@ -18,7 +21,14 @@ __global__ void __launch_bounds__(256) countHitsKernel(const int4* __restrict__ 
     if (threadIdx.x == 0) {
         unsigned long long t = 0;
         for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += s[w];
-        if (t) atomicAdd(out, t);
+        if (t) atomicAdd(&state[0], t);
+        __threadfence();
+        if (atomicAdd(&state[1], 1ull) == (unsigned long long)gridDim.x - 1) {
+            __threadfence();
+            *hostOut = atomicExch(&state[0], 0ull);
+            state[1] = 0;
+            __threadfence_system();
+        }
     }
 }
 
@@ -91,16 +101,15 @@ int b2rt_count_hits(b2rt_ctx* ctx, const void* results, int64_t n, int64_t* hits
     if (n == 0) return B2RT_OK;
     B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    unsigned long long* out = reinterpret_cast<unsigned long long*>(ctx->countDev);
-    B2RT_CUDA(ctx, cudaMemsetAsync(out, 0, sizeof(unsigned long long), s));
+    unsigned long long* state = reinterpret_cast<unsigned long long*>(ctx->countDev);
     long long grid = (n + 255) / 256;
     const long long cap = (long long)ctx->smCount * 8;
     if (grid > cap) grid = cap;
-    countHitsKernel<<<(unsigned)grid, 256, 0, s>>>(static_cast<const int4*>(results), n, out);
+    countHitsKernel<<<(unsigned)grid, 256, 0, s>>>(static_cast<const int4*>(results), n, state,
+                                                   reinterpret_cast<unsigned long long*>(ctx->countHost));
     B2RT_CHECK_LAUNCH(ctx, "countHitsKernel");
-    unsigned long long h = 0;
-    B2RT_CUDA(ctx, cudaMemcpyAsync(&h, out, sizeof(h), cudaMemcpyDeviceToHost, s));
     B2RT_CUDA(ctx, cudaStreamSynchronize(s));
+    const unsigned long long h = *reinterpret_cast<volatile unsigned long long*>(ctx->countHost);
     *hits = (int64_t)h;
     return B2RT_OK;
 }
