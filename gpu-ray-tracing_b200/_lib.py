@@ -59,7 +59,6 @@ _SIGNATURES = {
     "b2rt_set_trace_config": (i32, [vp, C.POINTER(TraceConfig)]),
     "b2rt_device_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
     "b2rt_set_bvh": (i32, [vp, vp, sz, vp, sz, vp, sz, i32, i32]),
-    "b2rt_private_nodes": (i32, [vp, sz, vp, sz, vp, sz, C.POINTER(sz), C.POINTER(i32), C.POINTER(i32)]),
     "b2rt_get_bvh": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]),
     "b2rt_trace": (i32, [vp, vp, vp, i64, C.c_uint, vp, C.POINTER(f32)]),
     "b2rt_trace_host": (i32, [vp, vp, vp, i64, C.c_uint, C.POINTER(f32), C.POINTER(f32)]),

@@ -90,56 +90,6 @@ static void relayoutNodes(const std::vector<float>& in, std::vector<float>& out,
     }
 }
 
-// Leaf references of the PRIVATE node array carry the leaf's triangle count: ~(row | count << kLeafRowBits), count in
-// 1..31, so the leaf loop knows its trip count when it starts (rows of the next triangle in flight while the current one is
-// tested, no terminator row fetched -- trace.cu).  The caller's arrays mark the end of a leaf with a terminator row only
-// (CudaBVH.cc:319-327).  A leaf with more than 31 triangles is cut into pieces behind appended private nodes whose two child
-// boxes both repeat the leaf's box: the pieces are visited in row order whenever the leaf would have been, so the same
-// triangles are tested in the same order.  Returns false (nothing packed) when a row index needs more than kLeafRowBits.
-static bool packLeafCounts(std::vector<float>& nodes, const float* woop, size_t woopRows)
-{
-    if (woopRows + kWoopPadBytes / 16 >= (size_t(1) << kLeafRowBits)) return false;
-    const size_t n0 = nodes.size() / 16;
-    auto countTris = [&](size_t row) -> int {
-        int n = 0;
-        while (row < woopRows) {
-            uint32_t x; memcpy(&x, woop + row * 4, 4);
-            if (x == 0x80000000u) break;
-            n++; row += 3;
-        }
-        return n;
-    };
-    auto packed = [](size_t row, int count) -> int32_t { return ~(int32_t)((uint32_t)row | ((uint32_t)count << kLeafRowBits)); };
-    for (size_t i = 0; i < n0; i++) {
-        for (int c = 0; c < 2; c++) {
-            int32_t ref; memcpy(&ref, &nodes[i * 16 + 12 + c], 4);
-            if (ref >= 0) continue;
-            size_t row = (size_t)(uint32_t)~ref;
-            int left = countTris(row);
-            if (left <= kLeafMaxCount) { ref = packed(row, left); memcpy(&nodes[i * 16 + 12 + c], &ref, 4); continue; }
-            // chain of appended nodes: child 0 = the next kLeafMaxCount triangles, child 1 = the rest
-            float box[6];       // lox hix loy hiy loz hiz of child c
-            { const float* p = &nodes[i * 16]; memcpy(box, p + 4 * c, 16); box[4] = p[8 + 2 * c]; box[5] = p[9 + 2 * c]; }
-            size_t parent = i; int slot = c;
-            while (left > kLeafMaxCount) {
-                const size_t fresh = nodes.size() / 16;
-                nodes.resize(nodes.size() + 16, 0.0f);
-                float* q = &nodes[fresh * 16];
-                memcpy(q, box, 16); memcpy(q + 4, box, 16);
-                q[8] = box[4]; q[9] = box[5]; q[10] = box[4]; q[11] = box[5];
-                int32_t ch[4] = { packed(row, kLeafMaxCount), 0, 0, 0 };
-                row += 3 * (size_t)kLeafMaxCount; left -= kLeafMaxCount;
-                if (left <= kLeafMaxCount) ch[1] = packed(row, left);
-                memcpy(q + 12, ch, 16);
-                const int32_t link = (int32_t)(fresh * 4);
-                memcpy(&nodes[parent * 16 + 12 + slot], &link, 4);
-                parent = fresh; slot = 1;
-            }
-        }
-    }
-    return true;
-}
-
 static void freeWide(b2rt_ctx* ctx)
 {
     cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
@@ -154,10 +104,9 @@ int ensureWide(b2rt_ctx* ctx)
 {
     if (ctx->hasWide) return B2RT_OK;
     if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
-    // the collapse reads plain Compact2 leaf references: the host copy kept by b2rt_set_bvh, not the packed device array
-    const std::vector<float>& nodes = ctx->hostNodes;
-    std::vector<float> woop(ctx->woopBytes / 4);
+    std::vector<float> nodes(ctx->nodeBytes / 4), woop(ctx->woopBytes / 4);
     std::vector<int32_t> tri(ctx->triIndexBytes / 4);
+    B2RT_CUDA(ctx, cudaMemcpy(nodes.data(), ctx->nodes, ctx->nodeBytes, cudaMemcpyDeviceToHost));
     if (ctx->woopBytes) B2RT_CUDA(ctx, cudaMemcpy(woop.data(), ctx->woop, ctx->woopBytes, cudaMemcpyDeviceToHost));
     if (ctx->triIndexBytes) B2RT_CUDA(ctx, cudaMemcpy(tri.data(), ctx->triIndex, ctx->triIndexBytes, cudaMemcpyDeviceToHost));
     Wide8 w;
@@ -231,6 +180,8 @@ void b2rt_destroy(b2rt_ctx* ctx)
     cudaFree(ctx->shareList); cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch);
     for (auto& slot : ctx->hostSlot) cudaFree(slot.stage);
     cudaFree(ctx->aabbDev); cudaFree(ctx->countDev); cudaFreeHost(ctx->countHost);
+    if (ctx->nodesTex) cudaDestroyTextureObject(ctx->nodesTex);
+    if (ctx->woopTex) cudaDestroyTextureObject(ctx->woopTex);
     if (ctx->sIn) {
         cudaStreamDestroy(ctx->sIn); cudaStreamDestroy(ctx->sRun); cudaStreamDestroy(ctx->sOut);
         for (auto& slot : ctx->hostSlot) {
@@ -281,20 +232,8 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     B2RT_CUDA(ctx, cudaMemcpy(in.data(), nodes, nodeBytes, srcIsDevice ? cudaMemcpyDeviceToHost : cudaMemcpyHostToHost));
     int topCount = 0;
     relayoutNodes(in, out, topCount);
-    ctx->hostNodes = out;                               // plain leaf references, for ensureWide
-    {
-        std::vector<float> woopHost;
-        const float* w = static_cast<const float*>(woop);
-        if (srcIsDevice && woopBytes) {
-            woopHost.resize(woopBytes / 4);
-            B2RT_CUDA(ctx, cudaMemcpy(woopHost.data(), woop, woopBytes, cudaMemcpyDeviceToHost));
-            w = woopHost.data();
-        }
-        ctx->leafCounts = packLeafCounts(out, w, woopBytes / 16);
-    }
-    ctx->privNodeBytes = out.size() * 4;
-    B2RT_CUDA(ctx, cudaMalloc(&ctx->nodes, ctx->privNodeBytes));
-    B2RT_CUDA(ctx, cudaMemcpy(ctx->nodes, out.data(), ctx->privNodeBytes, cudaMemcpyHostToDevice));
+    B2RT_CUDA(ctx, cudaMalloc(&ctx->nodes, nodeBytes));
+    B2RT_CUDA(ctx, cudaMemcpy(ctx->nodes, out.data(), nodeBytes, cudaMemcpyHostToDevice));
     // Woop rows: the leaf loop fetches three rows before it looks at the terminator, so the copy
     // carries padding rows past the last terminator (the reference relies on texture fetches
     // returning zero out of range, kepler_dynamic_fetch.cu:328-334).  The first padding row is
@@ -312,26 +251,22 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     if (triIndexBytes) B2RT_CUDA(ctx, cudaMemcpy(ctx->triIndex, triIndex, triIndexBytes, kind));
     ctx->nodeBytes = nodeBytes; ctx->woopBytes = woopBytes; ctx->triIndexBytes = triIndexBytes;
     ctx->topNodesAvail = topCount;
-    ctx->hasBvh = true;
-    return B2RT_OK;
-}
-
-int b2rt_private_nodes(const void* nodes, size_t nodeBytes, const void* woop, size_t woopBytes, void* out, size_t outCap,
-                       size_t* outBytes, int* topCount, int* counted)
-{
-    if (!nodes || nodeBytes < 64 || nodeBytes % 64 || woopBytes % 16 || (!woop && woopBytes) || !outBytes) return B2RT_ERR_ARG;
-    std::vector<float> in(nodeBytes / 4), priv;
-    memcpy(in.data(), nodes, nodeBytes);
-    int top = 0;
-    relayoutNodes(in, priv, top);
-    const bool packed = packLeafCounts(priv, static_cast<const float*>(woop), woopBytes / 16);
-    *outBytes = priv.size() * 4;
-    if (topCount) *topCount = top;
-    if (counted) *counted = packed ? 1 : 0;
-    if (out) {
-        if (outCap < priv.size() * 4) return B2RT_ERR_ARG;
-        memcpy(out, priv.data(), priv.size() * 4);
+    // linear float4 texture views (1D linear textures address up to 2^27 texels = 2 GB of float4; larger arrays keep 0)
+    for (int k = 0; k < 2; k++) {
+        cudaTextureObject_t& t = k ? ctx->woopTex : ctx->nodesTex;
+        if (t) { cudaDestroyTextureObject(t); t = 0; }
+        const size_t bytes = k ? woopBytes + kWoopPadBytes : nodeBytes;
+        if (bytes / 16 > (size_t(1) << 27) || bytes == 0) continue;
+        cudaResourceDesc rd; memset(&rd, 0, sizeof(rd));
+        rd.resType = cudaResourceTypeLinear;
+        rd.res.linear.devPtr = k ? (void*)ctx->woop : (void*)ctx->nodes;
+        rd.res.linear.desc = cudaCreateChannelDesc<float4>();
+        rd.res.linear.sizeInBytes = bytes;
+        cudaTextureDesc td; memset(&td, 0, sizeof(td));
+        td.readMode = cudaReadModeElementType;
+        B2RT_CUDA(ctx, cudaCreateTextureObject(&t, &rd, &td, nullptr));
     }
+    ctx->hasBvh = true;
     return B2RT_OK;
 }
 
@@ -340,7 +275,7 @@ int b2rt_get_bvh(const b2rt_ctx* ctx, const void** nodes, size_t* nodeBytes, con
 {
     if (!ctx || !ctx->hasBvh) return B2RT_ERR_NO_BVH;
     if (nodes) *nodes = ctx->nodes;
-    if (nodeBytes) *nodeBytes = ctx->privNodeBytes;
+    if (nodeBytes) *nodeBytes = ctx->nodeBytes;
     if (woop) *woop = ctx->woop;
     if (woopBytes) *woopBytes = ctx->woopBytes;
     if (triIndex) *triIndex = ctx->triIndex;

@@ -6,7 +6,6 @@
 #include <stdio.h>
 #include <string.h>
 #include <string>
-#include <vector>
 
 #include "../../include/b2rt.h"
 
@@ -24,8 +23,6 @@ static_assert(sizeof(Ray) == 32 && sizeof(RayResult) == 16 && sizeof(MortonKey) 
 
 constexpr int kSentinel = B2RT_ENTRYPOINT_SENTINEL;
 constexpr int kTimelineWarps = 8192;    // per-warp exit times kept by the instrumented kernel (statsDev[16 ...])
-constexpr int kLeafRowBits = 26;        // private leaf reference: ~(first Woop row | triangle count << 26)   (api.cu:packLeafCounts)
-constexpr int kLeafMaxCount = 31;
 constexpr size_t kWoopPadBytes = 64;   // private Woop copy: one terminator row + three zero rows past the caller's rows
 
 }  // namespace b2rt
@@ -43,10 +40,8 @@ struct b2rt_ctx {
     float4* nodes = nullptr;   size_t nodeBytes = 0;
     float4* woop = nullptr;    size_t woopBytes = 0;
     int32_t* triIndex = nullptr; size_t triIndexBytes = 0;
+    cudaTextureObject_t nodesTex = 0, woopTex = 0;      // linear float4 views of the two arrays (texture-pipe variants)
     int topNodesAvail = 0;     // how many leading nodes are in breadth-first order
-    size_t privNodeBytes = 0;  // bytes of the private node array (nodeBytes + nodes appended for leaves of more than 31 triangles)
-    bool leafCounts = false;   // its leaf references carry triangle counts
-    std::vector<float> hostNodes;   // the re-laid nodes with the caller's plain leaf references (input of the 8-wide collapse)
     bool hasBvh = false;
 
     // second private form: 8-wide compressed nodes + re-packed Woop rows (wide_bvh.h), built on first use

@@ -36,14 +36,15 @@ struct TraceParams {
     int pfNodeLines, pfWoopLines;   // 128-byte lines of the node / Woop arrays to pull into L2 when the launch starts (0 = none)
     int* warpCounter;
     unsigned long long* stats;
-    unsigned leafRowMask;   // row bits of a leaf reference: 2^26 - 1 when the references carry counts, all ones otherwise
+    cudaTextureObject_t nodesTex, woopTex;  // the same arrays behind the texture pipe (TEX variants)
 };
 
 constexpr int kLocalStack = 64;     // SplitBVHBuilder MaxDepth = 64 bounds the stack (SplitBVHBuilder.hh:43)
 constexpr unsigned kFull = 0xffffffffu;
 
-// MODE bit 2: the leaf loop ignores the triangle counts in the private leaf references and runs to the terminator row, as
-// the reference does (the form measured against; also what a BVH with more than 2^26 Woop rows gets).
+// TEX bit 0: node fetches outside the shared-memory top go through the texture pipe; bit 1: Woop rows do.
+// The L1 data is the same, but texture fetches use l1tex's TEX data pipe instead of the LSU data pipe that
+// ncu shows near saturation (l1tex__data_pipe_lsu_wavefronts 69-74 % of peak on the diffuse batch).
 // SHARE (compiled into the ANY_HIT kernels): subtree sharing in the tail of a launch.  Once the work counter has run dry a
 // launch is a set of dependent chains -- every remaining ray needs its remaining node visits one after the other, ~380 ns
 // each -- while most lanes and warps of the SM have nothing left to do (C3 AO batches: pool empty at 285 us, last warp at
@@ -66,7 +67,7 @@ constexpr int kShareRounds = 4;     // stack entries a lane may hand over per vi
 constexpr int kShareQueue = 128;    // queue entries (int4: ray, stack entry, hit distance); 2 KB keeps the L1 carve-out where it was
 constexpr int kShareList = 1024;    // shared rays per CTA (global memory, one slice per CTA and launch slot)
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int MODE>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
     extern __shared__ float4 s_dyn[];
@@ -99,7 +100,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
     }
     // SHARE: [ShareArea][queue] behind the planes
     constexpr bool SHARE = ANY_HIT;
-    constexpr bool COUNTED = !(MODE & 4);   // leaf references carry triangle counts
     constexpr int kQueue = kShareQueue, kListCap = kShareList, kWarps = BLOCK / 32;
     ShareArea* s_share = reinterpret_cast<ShareArea*>(reinterpret_cast<char*>(s_plane) + (size_t)topNodes * 56);
     int4* s_queue = reinterpret_cast<int4*>(s_share + 1);
@@ -331,6 +331,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     n0xy = lds128(a); n1xy = lds128(a + planeBytes); nz = lds128(a + 2u * planeBytes);
                     const int2 ch = lds64i(sTop + 3u * planeBytes + ((unsigned)nodeAddr << 1));
                     c0 = ch.x; c1 = ch.y;
+                } else if (TEX & 1) {
+                    n0xy = tex1Dfetch<float4>(p.nodesTex, nodeAddr); n1xy = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 1);
+                    nz = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 2);
+                    const float4 cn = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 3);
+                    c0 = __float_as_int(cn.x); c1 = __float_as_int(cn.y);
                 } else {
                     const float4* np = p.nodes + nodeAddr;
                     n0xy = ldg4(np); n1xy = ldg4(np + 1); nz = ldg4(np + 2);
@@ -373,11 +378,17 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 
             // postponed leaves
             while (leafAddr < 0) {
-                const unsigned leafRef = ~(unsigned)leafAddr;
-                int triAddr = (int)(leafRef & (COUNTED ? (1u << kLeafRowBits) - 1u : p.leafRowMask));
-                // one Woop test; true = leave the leaf loop (any-hit ray has its hit)
-                auto testTri = [&](const float4& v00, const float4& v11, const float4& v22) -> bool {
+                for (int triAddr = ~leafAddr;; triAddr += 3) {
+                    float4 v00, v11, v22;
+                    if (TEX & 2) {
+                        v00 = tex1Dfetch<float4>(p.woopTex, triAddr); v11 = tex1Dfetch<float4>(p.woopTex, triAddr + 1);
+                        v22 = tex1Dfetch<float4>(p.woopTex, triAddr + 2);
+                    } else {
+                        v00 = ldg4(p.woop + triAddr); v11 = ldg4(p.woop + triAddr + 1); v22 = ldg4(p.woop + triAddr + 2);
+                    }
+                    if (__float_as_int(v00.x) == (int)0x80000000) break;       // leaf terminator
                     if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
+
                     const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
                     const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
                     const float t = __fmul_rn(Oz, invDz);
@@ -392,45 +403,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                             if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
                                 hitT = t; hitIndex = triAddr;
                                 if (BARY) { hitU = u; hitV = v; }
-                                if (ANY_HIT) { nodeAddr = kSentinel; return true; }
+                                if (ANY_HIT) { nodeAddr = kSentinel; break; }
                             }
                         }
-                    }
-                    return false;
-                };
-                if (COUNTED && (MODE & 8)) {
-                    // counted, one register set: no terminator fetch, but each triangle's rows are requested only after the
-                    // previous triangle's have arrived (fewer registers)
-                    int left = (int)(leafRef >> kLeafRowBits);
-                    for (; left > 0; left--, triAddr += 3) {
-                        const float4 v00 = ldg4(p.woop + triAddr), v11 = ldg4(p.woop + triAddr + 1), v22 = ldg4(p.woop + triAddr + 2);
-                        if (testTri(v00, v11, v22)) break;
-                    }
-                } else if (COUNTED) {
-                    // The private leaf reference carries the triangle count (api.cu:packLeafCounts): no terminator row is
-                    // fetched, and the rows of triangle k+1 are in flight while triangle k is tested -- a leaf costs one
-                    // memory round trip plus its arithmetic instead of one round trip per triangle and one for the terminator.
-                    // Two register sets, A and B, used in turn (the loop is unrolled by hand so that the loads of the next
-                    // triangle are ISSUED before the first instruction that waits for the current one's rows; with a single
-                    // set and a copy at the end of the iteration ptxas rotates the copy to the top and the loads behind it).
-                    int left = (int)(leafRef >> kLeafRowBits);
-                    const float4* tp = p.woop + triAddr;
-                    float4 a00, a11, a22, b00, b11, b22;
-                    if (left > 0) { a00 = ldg4(tp); a11 = ldg4(tp + 1); a22 = ldg4(tp + 2); }
-                    while (left > 0) {
-                        if (left > 1) { b00 = ldg4(tp + 3); b11 = ldg4(tp + 4); b22 = ldg4(tp + 5); }
-                        if (testTri(a00, a11, a22)) break;
-                        if (left == 1) break;
-                        triAddr += 3;
-                        if (left > 2) { a00 = ldg4(tp + 6); a11 = ldg4(tp + 7); a22 = ldg4(tp + 8); }
-                        if (testTri(b00, b11, b22)) break;
-                        triAddr += 3; tp += 6; left -= 2;
-                    }
-                } else {
-                    for (;; triAddr += 3) {
-                        const float4 v00 = ldg4(p.woop + triAddr), v11 = ldg4(p.woop + triAddr + 1), v22 = ldg4(p.woop + triAddr + 2);
-                        if (__float_as_int(v00.x) == (int)0x80000000) break;       // leaf terminator
-                        if (testTri(v00, v11, v22)) break;
                     }
                 }
                 // a second leaf may be sitting in nodeAddr
@@ -511,10 +486,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 // ---------------------------------------------------------------------------------------------
 struct Variant { int block; int stackSmem; int minBlocks; };
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int MODE>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
-    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>;
+    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>;
     // any-hit kernels carry the sharing queue behind the staged nodes; the small-CTA default gives up 40 nodes for it so
     // that four CTAs still fit the 164 KB shared-memory step (the next step, 196 KB, costs 32 KB of L1)
     constexpr size_t shareBytes = ANY_HIT ? sizeof(ShareArea) + (size_t)kShareQueue * sizeof(int4) : 0;
@@ -552,20 +527,20 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int MODE = 0>
+template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX = 0>
 static int launchFlags(b2rt_ctx* ctx, TraceParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS) {
         // the instrumented build always writes barycentrics (one kernel fewer to carry)
-        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream)
-                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream);
+        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
     }
-    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream)
-                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream);
-    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream)
-                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream);
+    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
+    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
+                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
 }
 
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
@@ -584,12 +559,12 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // off unless asked for: measured on C2 (32 MB of BVH) it buys +0.3 % behind an L2 flush and costs 1-2 % when
         // the arrays are already resident (profiles/README.md)
         const bool on = ctx->cfg.l2_prefetch > 0;
-        p.pfNodeLines = on ? (int)std::min<size_t>(ctx->privNodeBytes / 128, 1u << 20) : 0;
+        p.pfNodeLines = on ? (int)std::min<size_t>(ctx->nodeBytes / 128, 1u << 20) : 0;
         p.pfWoopLines = on ? (int)std::min<size_t>(ctx->woopBytes / 128, 1u << 20) : 0;
     }
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
-    p.leafRowMask = ctx->leafCounts ? (1u << kLeafRowBits) - 1u : ~0u;
+    p.nodesTex = ctx->nodesTex; p.woopTex = ctx->woopTex;
     p.dummyLeaf = ~(int)(ctx->woopBytes / 16);       // first padding row: a terminator (api.cu:b2rt_set_bvh)
     p.shareList = nullptr;
     if (flags & B2RT_TRACE_STATS) {
@@ -610,7 +585,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // Mrays/s.  It is built on first use (host collapse of the private copy, api.cu:ensureWide).
         if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 104;
     }
-    if (!ctx->leafCounts && variant < 100) variant = (variant == 6 || variant == 8) ? 8 : 9;    // no counts to rely on
+    if (variant >= 8 && variant <= 9 && (!ctx->nodesTex || !ctx->woopTex)) variant = 6;   // array too large for a 1D texture
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {
     default:
@@ -622,11 +597,8 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     case 5: return launchFlags<12, 256, 6>(ctx, p, flags, stream);   // <= 40 regs, 48 warps/SM
     case 6: return launchFlags<12, 1024, 1>(ctx, p, flags, stream);  // one CTA per SM: one big shared top-of-tree
     case 7: return launchFlags<12, 512, 2>(ctx, p, flags, stream);   // two CTAs per SM, <= 64 regs
-    case 8: return launchFlags<12, 1024, 1, 4>(ctx, p, flags, stream);  // v6 with the terminator-driven leaf loop
-    case 9: return launchFlags<12, 256, 4, 4>(ctx, p, flags, stream);   // v1 with the terminator-driven leaf loop
-    case 10: return launchFlags<12, 512, 2, 4>(ctx, p, flags, stream);  // v7 with the terminator-driven leaf loop
-    case 11: return launchFlags<12, 512, 2, 8>(ctx, p, flags, stream);  // v7, counted leaves without the second register set
-    case 12: return launchFlags<12, 1024, 1, 8>(ctx, p, flags, stream); // v6, counted leaves without the second register set
+    case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // v6 with nodes through the texture pipe
+    case 9: return launchFlags<12, 1024, 1, 2>(ctx, p, flags, stream);  // v6 with Woop rows through the texture pipe
     }
 }
 
@@ -636,7 +608,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
 // postponement (kepler_dynamic_fetch.cu:204-408 reduced to its scalar algorithm), one thread per
 // ray, IEEE division -- counts, does not store hits
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict__ rays, int numRays, int anyHit, int counted,
+__global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict__ rays, int numRays, int anyHit,
                                                        const float4* __restrict__ nodes, const float4* __restrict__ woop,
                                                        unsigned long long* out)
 {
@@ -683,12 +655,9 @@ __global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict_
             } else {
                 cL++;
                 bool done = false;
-                // private leaf reference: ~(row | count << 26) when `counted`, the caller's ~row otherwise
-                const unsigned leafRef = ~(unsigned)nodeAddr;
-                int left = counted ? (int)(leafRef >> kLeafRowBits) : 0x7fffffff;
-                for (int triAddr = (int)(counted ? leafRef & ((1u << kLeafRowBits) - 1u) : leafRef); left > 0; triAddr += 3, left--) {
+                for (int triAddr = ~nodeAddr;; triAddr += 3) {
                     const float4 v00 = ldg4(woop + triAddr);
-                    if (!counted && __float_as_int(v00.x) == (int)0x80000000) break;
+                    if (__float_as_int(v00.x) == (int)0x80000000) break;
                     const float4 v11 = ldg4(woop + triAddr + 1), v22 = ldg4(woop + triAddr + 2);
                     cT++;
                     const float Oz = __fmaf_rn(-o.z, v00.z, __fmaf_rn(-o.y, v00.y, __fmaf_rn(-o.x, v00.x, v00.w)));
@@ -731,7 +700,7 @@ __global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict_
 int countWork(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, cudaStream_t stream)
 {
     B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
-    countWorkKernel<<<(unsigned)((numRays + 255) / 256), 256, 0, stream>>>(static_cast<const float4*>(rays), (int)numRays, anyHit, ctx->leafCounts ? 1 : 0,
+    countWorkKernel<<<(unsigned)((numRays + 255) / 256), 256, 0, stream>>>(static_cast<const float4*>(rays), (int)numRays, anyHit,
                                                                           ctx->nodes, ctx->woop, ctx->statsDev);
     B2RT_CHECK_LAUNCH(ctx, "countWorkKernel");
     unsigned long long h[8];

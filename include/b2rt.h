@@ -107,16 +107,7 @@ int  b2rt_device_info(const b2rt_ctx* ctx, int* sm_count, int* cc_major, int* cc
 int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t node_bytes, const void* woop,
                  size_t woop_bytes, const int32_t* tri_index, size_t tri_index_bytes, int layout,
                  int src_is_device);
-/* Host only, no device needed: the PRIVATE node array b2rt_set_bvh derives from the caller's Compact2 nodes (host pointers
- * in, host buffer out; out == NULL just returns the size).  Two changes against CudaBVH.hh:41-44: (1) the `*top_count` nodes
- * with the largest boxes come first (staged in shared memory by the kernel), inner child indices rewritten accordingly;
- * (2) a leaf reference is ~(first Woop row | triangle count << 26) with count in 1..31 instead of ~row, so the leaf loop
- * knows its trip count without fetching the terminator row (CudaBVH.cc:319-327); a leaf of more than 31 triangles is cut
- * into pieces behind appended nodes that repeat its box.  *counted = 0 when the Woop array has 2^26 rows or more: the
- * references then stay plain.  Woop rows and triIndex are never re-laid: hit indices address the caller's rows. */
-int b2rt_private_nodes(const void* nodes, size_t node_bytes, const void* woop, size_t woop_bytes, void* out,
-                       size_t out_capacity, size_t* out_bytes, int* top_count, int* counted);
-/* the arrays the kernels read (device pointers; the node array is the private form described above) */
+/* the arrays the kernels read (device pointers; the node array is the re-laid private copy) */
 int b2rt_get_bvh(const b2rt_ctx* ctx, const void** nodes_dev, size_t* node_bytes,
                  const void** woop_dev, size_t* woop_bytes, const int32_t** tri_index_dev,
                  size_t* tri_index_bytes);
