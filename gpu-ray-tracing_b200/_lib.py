@@ -69,6 +69,8 @@ _SIGNATURES = {
     "b2rt_raygen_primary": (i32, [vp, vp, vp, i32, i32, f32, vp, vp, vp, vp, vp]),
     "b2rt_raygen_ao": (i32, [vp, i32, i32, i32, f32, u32, vp, vp, vp, vp, vp, vp, vp]),
     "b2rt_morton_sort": (i32, [vp, vp, vp, vp, i64, vp, vp]),
+    "b2rt_set_sort_mode": (i32, [vp, i32]),
+    "b2rt_sort_fell_back": (i32, [vp]),
     "b2rt_find_aabb": (i32, [vp, vp, i64, vp, vp]),
     "b2rt_morton_keys": (i32, [vp, vp, i64, vp, vp, vp]),
     "b2rt_reorder_rays": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, vp]),

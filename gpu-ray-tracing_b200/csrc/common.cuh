@@ -70,6 +70,9 @@ struct b2rt_ctx {
     } hostSlot[kHostSlots];
     int nextHostSlot = 0;
 
+    int sortMode = 0;          // b2rt_set_sort_mode: 0 = prefix sort + tie settling (falls back by itself), 1 = always the full LSD sort
+    int sortFellBack = 0;      // the last b2rt_morton_sort went the long way
+
     // scratch (grown on demand, never shrunk)
     void* scratch = nullptr;  size_t scratchBytes = 0;
     int* shareList = nullptr; size_t shareListCtas = 0; // any-hit kernels: shared-ray lists, one slice per CTA (trace.cu)

@@ -12,11 +12,15 @@
 //     compile-time shifts in registers, no shared-memory read-modify-writes.  Stored as three
 //     64-bit words (lo/mid/hi) for the sort and, for b2rt_morton_keys, as the reference's 28-byte
 //     MortonKey records.
-//  3. Stable LSD radix sort, 8 bits per pass, over the 192-bit key carried as (64-bit word,
-//     32-bit slot) pairs: 8 passes on the low word, gather the middle word, 8 passes, gather the
-//     high word, and as many passes as it has significant bits (keys of in-range rays end at bit
-//     155).  Each pass = block histograms, one scan kernel (one CTA per bin), a stable scatter
-//     that ranks with __match_any_sync -- no atomics on the data path.
+//  3. Sort by a PREFIX of the key, then settle the ties.  Keys of in-range rays end at bit 146 (origin bit 24 at 6*24+2);
+//     the prefix is key >> kPrefixShift, saturated -- a monotone function of the key, so sorting by (prefix, key) is
+//     sorting by the key.  (a) stable LSD radix sort of (prefix, slot) pairs, 8 bits per pass, kPrefixPasses passes: block
+//     histograms, one scan kernel (one CTA per bin), a stable scatter that ranks with ballots -- no atomics on the data
+//     path; (b) one thread per run of equal prefixes orders the run's slots by the full 192-bit key (stable insertion
+//     sort; the words are gathered through the slots).  A run longer than kMaxRun (thousands of rays with one origin and
+//     direction cell) raises a flag and the call falls back to (c): the full LSD sort over all three 64-bit words -- 8 + 8
+//     passes and as many as the high word has significant bytes -- which is what every call did before (20 passes,
+//     0.82 ms per 2 Mi rays).
 //  4. Gather of rays by sorted slot + rebuild of idToSlot / slotToID (reorderRaysKernel).
 // Compiled with -fmad=false so the quantised components are bit-identical to the CPU oracle.
 #include "common.cuh"
@@ -90,10 +94,24 @@ __device__ __forceinline__ void scatterBits(unsigned (&hash)[6], unsigned v)
     }
 }
 
+// Prefix of the 192-bit key the first stage sorts by: bits kPrefixShift .. 146, kPrefixPasses bytes wide.
+constexpr int kKeyTopBit = 146;
+constexpr int kPrefixShift = 83;                                            // 64 <= shift < 128
+constexpr int kPrefixPasses = (kKeyTopBit + 1 - kPrefixShift + 7) / 8;      // 8
+constexpr int kMaxRun = 48;                                                 // longest run of equal prefixes settled by one thread
+static_assert(kPrefixShift >= 64 && kPrefixShift < 128 && kPrefixPasses >= 1 && kPrefixPasses <= 8, "prefix lies in the middle/high words");
+
+__device__ __forceinline__ u64 keyPrefix(u64 mid, u64 hi)
+{
+    const u64 all = (kPrefixPasses == 8) ? ~0ull : ((1ull << (8 * kPrefixPasses)) - 1ull);
+    if (hi >> (kKeyTopBit + 1 - 128)) return all;          // out-of-range ray (bits above 146): after every in-range key
+    return ((mid >> (kPrefixShift - 64)) | (hi << (128 - kPrefixShift))) & all;
+}
+
 // box: ordered-uint AABB (device) ; boxF: optional float AABB (for b2rt_morton_keys)
 template <bool AOS>
 __global__ void __launch_bounds__(256) mortonKeysKernel(const float4* __restrict__ rays, int n, const unsigned* box,
-                                                        const float* boxF, u64* lo, u64* mid, u64* hi,
+                                                        const float* boxF, u64* lo, u64* mid, u64* hi, u64* prefix,
                                                         unsigned* slots, MortonKey* keysAos)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -127,6 +145,7 @@ __global__ void __launch_bounds__(256) mortonKeysKernel(const float4* __restrict
         lo[i] = (u64)hash[0] | ((u64)hash[1] << 32);
         mid[i] = (u64)hash[2] | ((u64)hash[3] << 32);
         hi[i] = (u64)hash[4] | ((u64)hash[5] << 32);
+        prefix[i] = keyPrefix((u64)hash[2] | ((u64)hash[3] << 32), (u64)hash[4] | ((u64)hash[5] << 32));
         slots[i] = (unsigned)i;
     }
 }
@@ -321,6 +340,42 @@ __global__ void __launch_bounds__(kScThreads) rsScatterKernel(const u64* __restr
     }
 }
 
+// Stage (b): runs of equal prefixes.  The thread at the head of a run of 2..kMaxRun elements orders the run's slots by the
+// full key (hi, mid, lo words gathered through the slots); the prefix sort was stable, so the run arrives in slot order and
+// a stable insertion sort leaves equal keys in slot order.  Longer runs set *tooLong (the caller then sorts the long way).
+__global__ void __launch_bounds__(256) settleRunsKernel(const u64* __restrict__ prefix, unsigned* slots, int n,
+                                                        const u64* __restrict__ lo, const u64* __restrict__ mid,
+                                                        const u64* __restrict__ hi, int* tooLong)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u64 p = prefix[i];
+    if (i > 0 && prefix[i - 1] == p) return;            // not the head of its run
+    if (i + 1 >= n || prefix[i + 1] != p) return;       // a run of one
+    int len = 2;
+    while (len <= kMaxRun && i + len < n && prefix[i + len] == p) len++;
+    if (len > kMaxRun) { *tooLong = 1; return; }
+    unsigned sl[kMaxRun];
+    u64 kh[kMaxRun], km[kMaxRun], kl[kMaxRun];
+    for (int j = 0; j < len; j++) {
+        const unsigned s = slots[i + j];
+        const u64 h = hi[s], m = mid[s], l = lo[s];
+        int k = j;
+        while (k > 0 && (kh[k - 1] > h || (kh[k - 1] == h && (km[k - 1] > m || (km[k - 1] == m && kl[k - 1] > l))))) {
+            kh[k] = kh[k - 1]; km[k] = km[k - 1]; kl[k] = kl[k - 1]; sl[k] = sl[k - 1];
+            k--;
+        }
+        kh[k] = h; km[k] = m; kl[k] = l; sl[k] = s;
+    }
+    for (int j = 0; j < len; j++) slots[i + j] = sl[j];
+}
+
+__global__ void __launch_bounds__(256) iotaKernel(unsigned* slots, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) slots[i] = (unsigned)i;
+}
+
 __global__ void __launch_bounds__(256) gatherWordKernel(const u64* __restrict__ word, const unsigned* __restrict__ slots, u64* out, int n)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -393,7 +448,7 @@ int b2rt_morton_keys(b2rt_ctx* ctx, const void* rays, int64_t n, const float aab
     float* boxF = ctx->aabbDev;     // 8 floats allocated; reuse as float box
     B2RT_CUDA(ctx, cudaMemcpyAsync(boxF, aabb, 6 * sizeof(float), cudaMemcpyHostToDevice, s));
     mortonKeysKernel<true><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(static_cast<const float4*>(rays), (int)n, nullptr, boxF,
-                                                                      nullptr, nullptr, nullptr, nullptr, static_cast<MortonKey*>(keys));
+                                                                      nullptr, nullptr, nullptr, nullptr, nullptr, static_cast<MortonKey*>(keys));
     B2RT_CHECK_LAUNCH(ctx, "mortonKeysKernel");
     B2RT_CUDA(ctx, cudaStreamSynchronize(s));   // aabb is a host pointer the caller may reuse
     return B2RT_OK;
@@ -429,7 +484,8 @@ int b2rt_morton_sort(b2rt_ctx* ctx, void* rays, int32_t* idToSlot, int32_t* slot
     unsigned* sB = reinterpret_cast<unsigned*>(base); base += slotB;
     unsigned* blockHist = reinterpret_cast<unsigned*>(base); base += histB;
     unsigned* binTotal = reinterpret_cast<unsigned*>(base);
-    u64* orWord = reinterpret_cast<u64*>(base + 2048); base += 4096;
+    u64* orWord = reinterpret_cast<u64*>(base + 2048);
+    int* flag = reinterpret_cast<int*>(base + 3072); base += 4096;
     float4* oldRays = reinterpret_cast<float4*>(base); base += rayB;
     int32_t* oldSlotToID = reinterpret_cast<int32_t*>(base);
 
@@ -438,50 +494,62 @@ int b2rt_morton_sort(b2rt_ctx* ctx, void* rays, int32_t* idToSlot, int32_t* slot
     if (rc) return rc;
     const unsigned g = (unsigned)((n + 255) / 256);
     mortonKeysKernel<false><<<g, 256, 0, s>>>(static_cast<const float4*>(rays), n, reinterpret_cast<unsigned*>(ctx->aabbDev), nullptr,
-                                             wLo, wMid, wHi, sA, nullptr);
+                                             wLo, wMid, wHi, kA, sA, nullptr);
     B2RT_CHECK_LAUNCH(ctx, "mortonKeysKernel");
 
-    // Keys of rays inside the AABB end at bit 155 (24+1 bits x 3 at stride 6, components 0-2), so
-    // the high word normally needs 4 passes; out-of-range input (NaN boxes etc.) may set more
-    // bits, so the pass count for each word comes from an OR-reduction of that word.
     unsigned* slotsCur = sA; unsigned* slotsAlt = sB;
-    const u64* words[3] = { wLo, wMid, wHi };
-    for (int w = 0; w < 3; w++) {
-        const u64* cur;
-        if (w == 0) cur = wLo;
-        else {
-            gatherWordKernel<<<g, 256, 0, s>>>(words[w], slotsCur, kA, n);
-            B2RT_CHECK_LAUNCH(ctx, "gatherWordKernel");
-            cur = kA;
-        }
+    // one LSD pass over byte `pass` of the words in `cur`; returns the buffer the pass wrote
+    auto radixPass = [&](const u64* cur, int pass, bool histTaken) -> const u64* {
         u64* outBuf = (cur == kA) ? kB : kA;
-        int passes = 8;
-        if (w == 2) {
-            // OR-reduce the high word to find its highest significant byte
-            B2RT_CUDA(ctx, cudaMemsetAsync(orWord, 0, 8, s));
-            rsHistKernel<<<numBlocks, kRsThreads, 0, s>>>(cur, n, 0, blockHist, numBlocks, orWord);
-            B2RT_CHECK_LAUNCH(ctx, "rsHistKernel");
-            u64 h = 0;
-            B2RT_CUDA(ctx, cudaMemcpyAsync(&h, orWord, 8, cudaMemcpyDeviceToHost, s));
-            B2RT_CUDA(ctx, cudaStreamSynchronize(s));
-            passes = 0;
-            while (h) { passes++; h >>= 8; }
-        }
-        for (int pass = 0; pass < passes; pass++) {
-            const int shift = pass * 8;
-            if (!(w == 2 && pass == 0)) {       // the w == 2 first histogram was taken above
-                rsHistKernel<<<numBlocks, kRsThreads, 0, s>>>(cur, n, shift, blockHist, numBlocks, nullptr);
-                B2RT_CHECK_LAUNCH(ctx, "rsHistKernel");
+        if (!histTaken) rsHistKernel<<<numBlocks, kRsThreads, 0, s>>>(cur, n, pass * 8, blockHist, numBlocks, nullptr);
+        rsScanKernel<<<kRsBins, 512, 0, s>>>(blockHist, numBlocks, binTotal);
+        rsScatterKernel<<<numBlocks, kScThreads, kRsTile * 12, s>>>(cur, slotsCur, outBuf, slotsAlt, n, pass * 8, blockHist, numBlocks, binTotal);
+        ctx->launches += histTaken ? 2 : 3;
+        unsigned* t = slotsCur; slotsCur = slotsAlt; slotsAlt = t;
+        return outBuf;
+    };
+
+    // (a) by prefix, (b) ties by the full key
+    int tooLong = 0;
+    if (ctx->sortMode != 1) {
+        const u64* cur = kA;
+        for (int pass = 0; pass < kPrefixPasses; pass++) cur = radixPass(cur, pass, false);
+        B2RT_CUDA(ctx, cudaGetLastError());
+        B2RT_CUDA(ctx, cudaMemsetAsync(flag, 0, sizeof(int), s));
+        settleRunsKernel<<<g, 256, 0, s>>>(cur, slotsCur, n, wLo, wMid, wHi, flag);
+        B2RT_CHECK_LAUNCH(ctx, "settleRunsKernel");
+        B2RT_CUDA(ctx, cudaMemcpyAsync(&tooLong, flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+        B2RT_CUDA(ctx, cudaStreamSynchronize(s));
+    }
+    ctx->sortFellBack = (ctx->sortMode == 1 || tooLong) ? 1 : 0;
+    if (ctx->sortFellBack) {
+        // (c) the long way: LSD over the whole key, word by word.  Keys of rays inside the AABB end at bit 146, so the high
+        // word normally needs 3 passes; out-of-range input (NaN boxes etc.) may set more bits, so its pass count comes from
+        // an OR-reduction of the word.
+        if (slotsCur != sA) { unsigned* t = slotsCur; slotsCur = slotsAlt; slotsAlt = t; }
+        iotaKernel<<<g, 256, 0, s>>>(slotsCur, n);
+        B2RT_CHECK_LAUNCH(ctx, "iotaKernel");
+        const u64* words[3] = { wLo, wMid, wHi };
+        for (int w = 0; w < 3; w++) {
+            const u64* cur = wLo;
+            if (w > 0) {
+                gatherWordKernel<<<g, 256, 0, s>>>(words[w], slotsCur, kA, n);
+                B2RT_CHECK_LAUNCH(ctx, "gatherWordKernel");
+                cur = kA;
             }
-            rsScanKernel<<<kRsBins, 512, 0, s>>>(blockHist, numBlocks, binTotal);
-            B2RT_CHECK_LAUNCH(ctx, "rsScanKernel");
-            rsScatterKernel<<<numBlocks, kScThreads, kRsTile * 12, s>>>(cur, slotsCur, outBuf, slotsAlt, n, shift, blockHist, numBlocks, binTotal);
-            B2RT_CHECK_LAUNCH(ctx, "rsScatterKernel");
-            const u64* done = outBuf;
-            outBuf = (done == kA) ? kB : kA;
-            // `cur` may be wLo on the very first pass; afterwards it ping-pongs between kA and kB
-            cur = done;
-            unsigned* t = slotsCur; slotsCur = slotsAlt; slotsAlt = t;
+            int passes = 8;
+            if (w == 2) {
+                B2RT_CUDA(ctx, cudaMemsetAsync(orWord, 0, 8, s));
+                rsHistKernel<<<numBlocks, kRsThreads, 0, s>>>(cur, n, 0, blockHist, numBlocks, orWord);
+                B2RT_CHECK_LAUNCH(ctx, "rsHistKernel");
+                u64 h = 0;
+                B2RT_CUDA(ctx, cudaMemcpyAsync(&h, orWord, 8, cudaMemcpyDeviceToHost, s));
+                B2RT_CUDA(ctx, cudaStreamSynchronize(s));
+                passes = 0;
+                while (h) { passes++; h >>= 8; }
+            }
+            for (int pass = 0; pass < passes; pass++) cur = radixPass(cur, pass, w == 2 && pass == 0);
+            B2RT_CUDA(ctx, cudaGetLastError());
         }
     }
 
@@ -492,6 +560,15 @@ int b2rt_morton_sort(b2rt_ctx* ctx, void* rays, int32_t* idToSlot, int32_t* slot
     if (aabbOut) return readAABB(ctx, aabbOut, s);
     return B2RT_OK;
 }
+
+int b2rt_set_sort_mode(b2rt_ctx* ctx, int mode)
+{
+    if (!ctx || mode < 0 || mode > 1) return setError(ctx, B2RT_ERR_ARG, "b2rt_set_sort_mode: mode must be 0 or 1");
+    ctx->sortMode = mode;
+    return B2RT_OK;
+}
+
+int b2rt_sort_fell_back(const b2rt_ctx* ctx) { return ctx ? ctx->sortFellBack : 0; }
 
 int b2rt_reorder_rays(b2rt_ctx* ctx, const void* keys, const void* inRays, const int32_t* inSlotToID, void* outRays,
                       int32_t* outIDToSlot, int32_t* outSlotToID, int64_t n, void* stream)

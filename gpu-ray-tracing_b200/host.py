@@ -66,6 +66,13 @@ class Context:
         cfg = TraceConfig(top_nodes, fetch_threshold, blocks_per_sm, variant, l2_prefetch)
         check(lib().b2rt_set_trace_config(self.handle, C.byref(cfg)), self.handle)
 
+    def set_sort_mode(self, mode=0):
+        """0 = prefix radix sort + tie settling (default), 1 = always the full 192-bit LSD sort (b2rt_set_sort_mode)."""
+        check(lib().b2rt_set_sort_mode(self.handle, int(mode)), self.handle)
+
+    def sort_fell_back(self):
+        return bool(lib().b2rt_sort_fell_back(self.handle))
+
     def torch_device(self):
         return torch.device("cuda", self.device)
 

@@ -166,11 +166,16 @@ int b2rt_raygen_ao(b2rt_ctx* ctx, int first_input_slot, int num_input_rays, int 
 /* replaces RayBuffer::mortonSort (ray/RayBuffer.cc:256-324) and its three launchers
  * (ray/RayBufferKernels.hh:112-117) plus the host quicksort (framework/base/Sort.cc:131-165):
  * AABB of origins and end points, 192-bit 6-D Morton key, device radix sort, gather of rays and
- * rebuild of both id maps -- all on the device, in place.  aabb_out (host, 6 floats lo/hi,
- * optional) makes the call synchronous.  Order inside runs of equal keys is unspecified, as in
- * the reference (unstable quicksort). */
+ * rebuild of both id maps -- all on the device, in place.  The call synchronises `stream` (it
+ * reads one flag back to decide between its two sort paths).  Order inside runs of equal keys is
+ * unspecified in the reference (unstable quicksort); here it is slot order (stable). */
 int b2rt_morton_sort(b2rt_ctx* ctx, void* rays_dev, int32_t* id_to_slot_dev,
                      int32_t* slot_to_id_dev, int64_t num_rays, float aabb_out[6], void* stream);
+/* Sort path: 0 (default) = radix sort by the key's top 64 significant bits, then ties settled by the full key; falls back
+ * by itself to 1 = radix sort over all 192 bits when a run of equal prefixes is too long.  Both give the same order.
+ * b2rt_sort_fell_back: 1 if the last b2rt_morton_sort went the long way. */
+int b2rt_set_sort_mode(b2rt_ctx* ctx, int mode);
+int b2rt_sort_fell_back(const b2rt_ctx* ctx);
 /* the pieces, for parity tests: AABB (RayBufferKernels.cu:74-140) and keys (:144-179) */
 int b2rt_find_aabb(b2rt_ctx* ctx, const void* rays_dev, int64_t num_rays, float aabb_out[6],
                    void* stream);

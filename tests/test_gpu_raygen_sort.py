@@ -121,6 +121,63 @@ def test_morton_sort(b2rt, oracle, ctx, n):
     assert got_keys.tobytes() == ref_keys.tobytes()
 
 
+def _sorted_like_the_oracle(b2rt, oracle, ctx, rays, mode):
+    """Sorts `rays` (identity ids) on the device with the given sort path; returns (fell_back, device rays, device
+    slotToID, oracle rays, oracle slotToID).  The oracle sorts stably and so do both device paths, so the permutation
+    itself must agree, not only the key sequence."""
+    rb = b2rt.RayBuffer()
+    rb.setRays(rays, np.arange(len(rays), dtype=np.int32))
+    ctx.set_sort_mode(mode)
+    try:
+        rb.mortonSort(ctx)
+        fell_back = ctx.sort_fell_back()
+    finally:
+        ctx.set_sort_mode(0)
+    ref_rays, _, ref_slot2id = oracle.morton_sort(rays)[:3]
+    return fell_back, rb.getRays(), rb.getSlotToIDBuffer_dev().cpu().numpy(), ref_rays, ref_slot2id
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_morton_sort_settles_prefix_ties_by_the_full_key(b2rt, oracle, ctx, mode):
+    """Rays that agree in the 64 key bits the first stage sorts by (same origin cell, directions 1e-5 apart) and differ
+    below them, mixed with exact duplicates (runs of 40 <= kMaxRun) and ordinary rays: both sort paths must return the
+    oracle's stable order."""
+    rng = np.random.default_rng(77)
+    n = 20000
+    rays = np.zeros(n, b2rt.RAY_DTYPE)
+    rays["o"] = rng.uniform(-2, 2, (n, 3)).astype(np.float32)
+    d = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    # groups of 12 rays: one origin, directions inside a 1e-5 cone
+    for g in range(600):
+        lo = 12 * g
+        rays["o"][lo:lo + 12] = rays["o"][lo]
+        d[lo:lo + 12] = d[lo] + rng.normal(0, 1e-5, (12, 3)).astype(np.float32)
+    rays["d"] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    rays["tmax"] = rng.uniform(0.1, 1.0, n).astype(np.float32)
+    rays[9000:9040] = rays[8999]                    # 41 identical rays: one run, ordered by slot
+    fell_back, got, slot2id, ref, ref_slot2id = _sorted_like_the_oracle(b2rt, oracle, ctx, rays, mode)
+    assert fell_back == (mode == 1)
+    assert got.tobytes() == ref.tobytes()
+    assert np.array_equal(slot2id, ref_slot2id)
+
+
+def test_morton_sort_falls_back_on_long_runs(b2rt, oracle, ctx):
+    """3 000 identical rays form one run of equal prefixes, longer than a thread settles: the call takes the full
+    192-bit sort by itself and still returns the oracle's order."""
+    rng = np.random.default_rng(78)
+    n = 30000
+    rays = np.zeros(n, b2rt.RAY_DTYPE)
+    rays["o"] = rng.uniform(-2, 2, (n, 3)).astype(np.float32)
+    d = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    rays["d"] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    rays["tmax"] = 1.0
+    rays[5000:8000] = rays[4999]
+    fell_back, got, slot2id, ref, ref_slot2id = _sorted_like_the_oracle(b2rt, oracle, ctx, rays, 0)
+    assert fell_back
+    assert got.tobytes() == ref.tobytes()
+    assert np.array_equal(slot2id, ref_slot2id)
+
+
 def test_count_hits_and_reconstruct(b2rt, oracle, ctx):
     scene, rg, prim, _, _ = _scene_and_primary(b2rt, oracle, ctx)
     bvh = b2rt.BVH(scene)

@@ -74,8 +74,16 @@ def main():
         sec.mortonSort(ctx)
     def restore_only():
         sec.m_rays[:nsec].copy_(rays0); sec.m_IDToSlot[:nsec].copy_(i2s0); sec.m_slotToID[:nsec].copy_(s2i0)
-    ms = timed(sort) - timed(restore_only)
-    report("mortonSort (AABB+keys+radix+reorder)", ms, nsec * (32 + 32 + 28 + 20 * (12 + 24) + 68 + 40), nsec, "rays")
+    t_restore = timed(restore_only)
+    # default path: 8 prefix passes + tie settling (3 x 8 B gathered per ray in a run); mode 1: the full 19-20-pass LSD sort
+    ms = timed(sort) - t_restore
+    fell = ctx.sort_fell_back()
+    report("mortonSort (AABB+keys+prefix radix+ties+reorder)%s" % (" FELL BACK" if fell else ""), ms,
+           nsec * (32 + 32 + 36 + 8 * (12 + 24) + 24 + 12 + 68 + 40), nsec, "rays")
+    ctx.set_sort_mode(1)
+    ms = timed(sort) - t_restore
+    ctx.set_sort_mode(0)
+    report("mortonSort, full 192-bit LSD (mode 1)", ms, nsec * (32 + 32 + 28 + 20 * (12 + 24) + 68 + 40), nsec, "rays")
 
     # a14 / f1
     ms = timed(lambda: b2rt.countHits(prim.getResultBuffer_dev(), ctx))
