@@ -171,8 +171,9 @@ int b2rt_raygen_ao(b2rt_ctx* ctx, int first_input_slot, int num_input_rays, int 
  * unspecified in the reference (unstable quicksort); here it is slot order (stable). */
 int b2rt_morton_sort(b2rt_ctx* ctx, void* rays_dev, int32_t* id_to_slot_dev,
                      int32_t* slot_to_id_dev, int64_t num_rays, float aabb_out[6], void* stream);
-/* Sort path: 0 (default) = radix sort by the key's top 64 significant bits, then ties settled by the full key; falls back
+/* Sort path: 0 (default) = radix sort by the key's top 56 significant bits, then ties settled by the full key; falls back
  * by itself to 1 = radix sort over all 192 bits when a run of equal prefixes is too long.  Both give the same order.
+ * A mode in 64..139 is path 0 with that prefix shift instead of the default 91 (tuning: (147 - shift) / 8 passes).
  * b2rt_sort_fell_back: 1 if the last b2rt_morton_sort went the long way. */
 int b2rt_set_sort_mode(b2rt_ctx* ctx, int mode);
 int b2rt_sort_fell_back(const b2rt_ctx* ctx);

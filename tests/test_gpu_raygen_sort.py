@@ -139,7 +139,7 @@ def _sorted_like_the_oracle(b2rt, oracle, ctx, rays, mode):
 
 @pytest.mark.parametrize("mode", [0, 1])
 def test_morton_sort_settles_prefix_ties_by_the_full_key(b2rt, oracle, ctx, mode):
-    """Rays that agree in the 64 key bits the first stage sorts by (same origin cell, directions 1e-5 apart) and differ
+    """Rays that agree in the 56 key bits the first stage sorts by (same origin cell, directions 1e-5 apart) and differ
     below them, mixed with exact duplicates (runs of 40 <= kMaxRun) and ordinary rays: both sort paths must return the
     oracle's stable order."""
     rng = np.random.default_rng(77)

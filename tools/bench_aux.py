@@ -75,11 +75,16 @@ def main():
     def restore_only():
         sec.m_rays[:nsec].copy_(rays0); sec.m_IDToSlot[:nsec].copy_(i2s0); sec.m_slotToID[:nsec].copy_(s2i0)
     t_restore = timed(restore_only)
-    # default path: 8 prefix passes + tie settling (3 x 8 B gathered per ray in a run); mode 1: the full 19-20-pass LSD sort
+    # default path: 7 prefix passes + tie settling (3 x 8 B gathered per ray in a run); mode 1: the full 19-20-pass LSD sort
     ms = timed(sort) - t_restore
     fell = ctx.sort_fell_back()
     report("mortonSort (AABB+keys+prefix radix+ties+reorder)%s" % (" FELL BACK" if fell else ""), ms,
-           nsec * (32 + 32 + 36 + 8 * (12 + 24) + 24 + 12 + 68 + 40), nsec, "rays")
+           nsec * (32 + 32 + 36 + 7 * (12 + 24) + 24 + 12 + 68 + 40), nsec, "rays")
+    for shift in (83, 99):
+        ctx.set_sort_mode(shift)
+        ms = timed(sort) - t_restore
+        report("mortonSort, prefix shift %d%s" % (shift, " FELL BACK" if ctx.sort_fell_back() else ""), ms,
+               nsec * (32 + 32 + 36 + ((147 - shift + 7) // 8) * (12 + 24) + 24 + 12 + 68 + 40), nsec, "rays")
     ctx.set_sort_mode(1)
     ms = timed(sort) - t_restore
     ctx.set_sort_mode(0)
