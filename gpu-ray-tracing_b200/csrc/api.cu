@@ -180,8 +180,6 @@ void b2rt_destroy(b2rt_ctx* ctx)
     cudaFree(ctx->shareList); cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch);
     for (auto& slot : ctx->hostSlot) cudaFree(slot.stage);
     cudaFree(ctx->aabbDev); cudaFree(ctx->countDev); cudaFreeHost(ctx->countHost);
-    if (ctx->nodesTex) cudaDestroyTextureObject(ctx->nodesTex);
-    if (ctx->woopTex) cudaDestroyTextureObject(ctx->woopTex);
     if (ctx->sIn) {
         cudaStreamDestroy(ctx->sIn); cudaStreamDestroy(ctx->sRun); cudaStreamDestroy(ctx->sOut);
         for (auto& slot : ctx->hostSlot) {
@@ -251,21 +249,6 @@ int b2rt_set_bvh(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void*
     if (triIndexBytes) B2RT_CUDA(ctx, cudaMemcpy(ctx->triIndex, triIndex, triIndexBytes, kind));
     ctx->nodeBytes = nodeBytes; ctx->woopBytes = woopBytes; ctx->triIndexBytes = triIndexBytes;
     ctx->topNodesAvail = topCount;
-    // linear float4 texture views (1D linear textures address up to 2^27 texels = 2 GB of float4; larger arrays keep 0)
-    for (int k = 0; k < 2; k++) {
-        cudaTextureObject_t& t = k ? ctx->woopTex : ctx->nodesTex;
-        if (t) { cudaDestroyTextureObject(t); t = 0; }
-        const size_t bytes = k ? woopBytes + kWoopPadBytes : nodeBytes;
-        if (bytes / 16 > (size_t(1) << 27) || bytes == 0) continue;
-        cudaResourceDesc rd; memset(&rd, 0, sizeof(rd));
-        rd.resType = cudaResourceTypeLinear;
-        rd.res.linear.devPtr = k ? (void*)ctx->woop : (void*)ctx->nodes;
-        rd.res.linear.desc = cudaCreateChannelDesc<float4>();
-        rd.res.linear.sizeInBytes = bytes;
-        cudaTextureDesc td; memset(&td, 0, sizeof(td));
-        td.readMode = cudaReadModeElementType;
-        B2RT_CUDA(ctx, cudaCreateTextureObject(&t, &rd, &td, nullptr));
-    }
     ctx->hasBvh = true;
     return B2RT_OK;
 }

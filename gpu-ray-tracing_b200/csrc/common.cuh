@@ -40,7 +40,6 @@ struct b2rt_ctx {
     float4* nodes = nullptr;   size_t nodeBytes = 0;
     float4* woop = nullptr;    size_t woopBytes = 0;
     int32_t* triIndex = nullptr; size_t triIndexBytes = 0;
-    cudaTextureObject_t nodesTex = 0, woopTex = 0;      // linear float4 views of the two arrays (texture-pipe variants)
     int topNodesAvail = 0;     // how many leading nodes are in breadth-first order
     bool hasBvh = false;
 

@@ -36,15 +36,15 @@ struct TraceParams {
     int pfNodeLines, pfWoopLines;   // 128-byte lines of the node / Woop arrays to pull into L2 when the launch starts (0 = none)
     int* warpCounter;
     unsigned long long* stats;
-    cudaTextureObject_t nodesTex, woopTex;  // the same arrays behind the texture pipe (TEX variants)
 };
 
 constexpr int kLocalStack = 64;     // SplitBVHBuilder MaxDepth = 64 bounds the stack (SplitBVHBuilder.hh:43)
 constexpr unsigned kFull = 0xffffffffu;
 
-// TEX bit 0: node fetches outside the shared-memory top go through the texture pipe; bit 1: Woop rows do.
-// The L1 data is the same, but texture fetches use l1tex's TEX data pipe instead of the LSU data pipe that
-// ncu shows near saturation (l1tex__data_pipe_lsu_wavefronts 69-74 % of peak on the diffuse batch).
+// LEAF: shape of the leaf loop.  0 = three rows per triangle fetched together, terminator tested on the fetched row 0, Woop
+// test with early-outs (the reference's shape, kepler_dynamic_fetch.cu:326-379).  1 = row 0 of the next triangle requested
+// ahead, test without early-outs (below).  Measured (profiles/r01_explore_c{2,3,5}_leaf_ahead.log): LEAF 1 wins on frame-sized
+// batches, C2 4 583 -> 4 753 and C3 2 753 -> 2 890 Mrays/s, and loses on the 64 Mi-ray incoherent batch, C5 3 001 -> 2 797.
 // SHARE (compiled into the ANY_HIT kernels): subtree sharing in the tail of a launch.  Once the work counter has run dry a
 // launch is a set of dependent chains -- every remaining ray needs its remaining node visits one after the other, ~380 ns
 // each -- while most lanes and warps of the SM have nothing left to do (C3 AO batches: pool empty at 285 us, last warp at
@@ -67,7 +67,7 @@ constexpr int kShareRounds = 4;     // stack entries a lane may hand over per vi
 constexpr int kShareQueue = 128;    // queue entries (int4: ray, stack entry, hit distance); 2 KB keeps the L1 carve-out where it was
 constexpr int kShareList = 1024;    // shared rays per CTA (global memory, one slice per CTA and launch slot)
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
     extern __shared__ float4 s_dyn[];
@@ -331,11 +331,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     n0xy = lds128(a); n1xy = lds128(a + planeBytes); nz = lds128(a + 2u * planeBytes);
                     const int2 ch = lds64i(sTop + 3u * planeBytes + ((unsigned)nodeAddr << 1));
                     c0 = ch.x; c1 = ch.y;
-                } else if (TEX & 1) {
-                    n0xy = tex1Dfetch<float4>(p.nodesTex, nodeAddr); n1xy = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 1);
-                    nz = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 2);
-                    const float4 cn = tex1Dfetch<float4>(p.nodesTex, nodeAddr + 3);
-                    c0 = __float_as_int(cn.x); c1 = __float_as_int(cn.y);
                 } else {
                     const float4* np = p.nodes + nodeAddr;
                     n0xy = ldg4(np); n1xy = ldg4(np + 1); nz = ldg4(np + 2);
@@ -378,32 +373,59 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 
             // postponed leaves
             while (leafAddr < 0) {
-                for (int triAddr = ~leafAddr;; triAddr += 3) {
-                    float4 v00, v11, v22;
-                    if (TEX & 2) {
-                        v00 = tex1Dfetch<float4>(p.woopTex, triAddr); v11 = tex1Dfetch<float4>(p.woopTex, triAddr + 1);
-                        v22 = tex1Dfetch<float4>(p.woopTex, triAddr + 2);
-                    } else {
-                        v00 = ldg4(p.woop + triAddr); v11 = ldg4(p.woop + triAddr + 1); v22 = ldg4(p.woop + triAddr + 2);
-                    }
-                    if (__float_as_int(v00.x) == (int)0x80000000) break;       // leaf terminator
-                    if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
-
-                    const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
-                    const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
-                    const float t = __fmul_rn(Oz, invDz);
-                    if (t > tmin && t < hitT) {
+                if (LEAF == 1) {
+                    // Row 0 of the NEXT triangle (or the terminator) is requested before the current triangle is tested: the
+                    // terminator test and the distance test of the next step need nothing else, so they no longer wait a whole
+                    // fetch behind the current test (ncu source page of the LEAF == 0 kernel: 14 % of all stall samples sit on the
+                    // terminator compares), and rows 1 and 2 behind the terminator are never read (two fetches fewer per leaf).
+                    // The Woop test runs without early-outs: with ~10 lanes in a triangle step one of them nearly always passes
+                    // the distance test, so the u and v stages run anyway -- and with conditional uses ptxas sinks the fetches
+                    // of rows 1 and 2 behind the distance test (three dependent fetches for a hit; measured slower).  Same
+                    // operations in the same order as LEAF == 0: the same bits.
+                    int triAddr = ~leafAddr;
+                    float4 v00 = ldg4(p.woop + triAddr);
+                    while (__float_as_int(v00.x) != (int)0x80000000) {
+                        const float4 n00 = ldg4(p.woop + triAddr + 3);
+                        const float4 v11 = ldg4(p.woop + triAddr + 1), v22 = ldg4(p.woop + triAddr + 2);
+                        if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
+                        const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
+                        const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
+                        const float t = __fmul_rn(Oz, invDz);
                         const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
                         const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
                         const float u = __fmaf_rn(t, Dx, Ox);
-                        if (u >= 0.0f) {
-                            const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
-                            const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
-                            const float v = __fmaf_rn(t, Dy, Oy);
-                            if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
-                                hitT = t; hitIndex = triAddr;
-                                if (BARY) { hitU = u; hitV = v; }
-                                if (ANY_HIT) { nodeAddr = kSentinel; break; }
+                        const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
+                        const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
+                        const float v = __fmaf_rn(t, Dy, Oy);
+                        if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                            hitT = t; hitIndex = triAddr;
+                            if (BARY) { hitU = u; hitV = v; }
+                            if (ANY_HIT) { nodeAddr = kSentinel; break; }
+                        }
+                        v00 = n00; triAddr += 3;
+                    }
+                } else {
+                    for (int triAddr = ~leafAddr;; triAddr += 3) {
+                        const float4 v00 = ldg4(p.woop + triAddr), v11 = ldg4(p.woop + triAddr + 1), v22 = ldg4(p.woop + triAddr + 2);
+                        if (__float_as_int(v00.x) == (int)0x80000000) break;       // leaf terminator
+                        if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
+
+                        const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
+                        const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
+                        const float t = __fmul_rn(Oz, invDz);
+                        if (t > tmin && t < hitT) {
+                            const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
+                            const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
+                            const float u = __fmaf_rn(t, Dx, Ox);
+                            if (u >= 0.0f) {
+                                const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
+                                const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
+                                const float v = __fmaf_rn(t, Dy, Oy);
+                                if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                                    hitT = t; hitIndex = triAddr;
+                                    if (BARY) { hitU = u; hitV = v; }
+                                    if (ANY_HIT) { nodeAddr = kSentinel; break; }
+                                }
                             }
                         }
                     }
@@ -486,10 +508,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 // ---------------------------------------------------------------------------------------------
 struct Variant { int block; int stackSmem; int minBlocks; };
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF>
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
-    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>;
+    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>;
     // any-hit kernels carry the sharing queue behind the staged nodes; the small-CTA default gives up 40 nodes for it so
     // that four CTAs still fit the 164 KB shared-memory step (the next step, 196 KB, costs 32 KB of L1)
     constexpr size_t shareBytes = ANY_HIT ? sizeof(ShareArea) + (size_t)kShareQueue * sizeof(int4) : 0;
@@ -527,20 +549,20 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int TEX = 0>
+template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF = 0>
 static int launchFlags(b2rt_ctx* ctx, TraceParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS) {
         // the instrumented build always writes barycentrics (one kernel fewer to carry)
-        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
-                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
+        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream)
+                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream);
     }
-    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
-                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
-    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream)
-                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, TEX>(ctx, p, stream);
+    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream)
+                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream);
+    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream)
+                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream);
 }
 
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
@@ -564,7 +586,6 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     }
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
-    p.nodesTex = ctx->nodesTex; p.woopTex = ctx->woopTex;
     p.dummyLeaf = ~(int)(ctx->woopBytes / 16);       // first padding row: a terminator (api.cu:b2rt_set_bvh)
     p.shareList = nullptr;
     if (flags & B2RT_TRACE_STATS) {
@@ -576,16 +597,15 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // measured on B200 (profiles/r01_explore_*_v2.log): one 1024-thread CTA per SM with a 2048-node shared top of
         // the tree wins on frame-sized batches (shorter tail, more node visits served from shared memory); four
         // 256-thread CTAs win on multi-million-ray batches
-        variant = (numRays <= (4 << 20)) ? 6 : 1;
+        variant = (numRays <= (4 << 20)) ? 8 : 1;
         // any-hit batches share subtrees inside a CTA once the pool is dry; two 512-thread CTAs per SM measured best
         // on C3's 2 Mi-ray AO batches (2 780 vs 2 710 Mrays/s for variant 6, 2 750 for variant 1)
-        if ((flags & B2RT_TRACE_ANY_HIT) && numRays <= (4 << 20)) variant = 7;
+        if ((flags & B2RT_TRACE_ANY_HIT) && numRays <= (4 << 20)) variant = 9;
         // a BVH several times the size of L2 (126 MB): most node visits go to DRAM, and the 8-wide compressed private form
         // (80 bytes per 8 children instead of 64 per 2, trace_wide.cu) wins -- C4, 1.2 GB of Compact2 arrays: 500 vs 425
         // Mrays/s.  It is built on first use (host collapse of the private copy, api.cu:ensureWide).
         if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 104;
     }
-    if (variant >= 8 && variant <= 9 && (!ctx->nodesTex || !ctx->woopTex)) variant = 6;   // array too large for a 1D texture
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {
     default:
@@ -593,12 +613,11 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     case 1: return launchFlags<12, 256, 4>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM
     case 2: return launchFlags<0, 256, 5>(ctx, p, flags, stream);    // stack entirely in local memory
     case 3: return launchFlags<16, 128, 8>(ctx, p, flags, stream);   // small CTAs
-    case 4: return launchFlags<8, 512, 3>(ctx, p, flags, stream);    // big CTAs, 48 warps/SM (<= 40 regs)
-    case 5: return launchFlags<12, 256, 6>(ctx, p, flags, stream);   // <= 40 regs, 48 warps/SM
     case 6: return launchFlags<12, 1024, 1>(ctx, p, flags, stream);  // one CTA per SM: one big shared top-of-tree
     case 7: return launchFlags<12, 512, 2>(ctx, p, flags, stream);   // two CTAs per SM, <= 64 regs
-    case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // v6 with nodes through the texture pipe
-    case 9: return launchFlags<12, 1024, 1, 2>(ctx, p, flags, stream);  // v6 with Woop rows through the texture pipe
+    case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // v6 with the look-ahead leaf loop
+    case 9: return launchFlags<12, 512, 2, 1>(ctx, p, flags, stream);   // v7 with the look-ahead leaf loop
+    case 10: return launchFlags<12, 256, 4, 1>(ctx, p, flags, stream);  // v1 with the look-ahead leaf loop
     }
 }
 

@@ -40,7 +40,7 @@ def _check_closest(oracle, bvh_arrays, rays, got, ref=None, agree=ID_AGREE):
 
 
 @pytest.mark.parametrize("kind,ntris", [("blob", 20000), ("interior", 30000), ("knot", 40000), ("strands", 30000)])
-@pytest.mark.parametrize("variant", [0, 2])
+@pytest.mark.parametrize("variant", [0, 2, 8, 10])
 def test_primary_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     scene = b2rt.Scene.generate(kind, ntris, 20260101)
     bvh = b2rt.BVH(scene)
@@ -168,7 +168,7 @@ def test_wide_kernel_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     assert (got["id"][5::97] == -1).all() and (got["t"][5::97] == -1.0).all()
 
 
-@pytest.mark.parametrize("variant", [6, 1, 3])
+@pytest.mark.parametrize("variant", [6, 1, 3, 9])
 @pytest.mark.parametrize("kind,ntris", [("interior", 30000), ("knot", 40000)])
 @pytest.mark.parametrize("count", [1, 37, 4097, 0])
 def test_any_hit_subtree_sharing(b2rt, oracle, ctx, kind, ntris, variant, count):
@@ -346,3 +346,39 @@ def test_traces_on_two_streams_overlap_safely(b2rt, oracle, ctx):
             if rb.getNeedClosestHit():
                 same = got["id"] == want["id"]
                 assert same.mean() >= 0.999 and (got["t"][same] == want["t"][same]).all()
+
+
+@pytest.mark.parametrize("pair", [(6, 8), (1, 10), (7, 9)])
+def test_lookahead_leaf_loop_returns_the_same_bits(b2rt, oracle, ctx, pair):
+    """LEAF = 1 (row 0 of the next triangle requested ahead, Woop test without early-outs; trace.cu) performs the same
+    floating-point operations in the same order as the reference-shaped loop: wherever both kernels report the same
+    triangle, t, u and v must be identical bit for bit, and the ids may differ only between triangles at one distance."""
+    scene = b2rt.Scene.generate("interior", 30000, 7)
+    bvh = b2rt.BVH(scene)
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.writeBarycentrics = True
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    origin, m = b2rt.camera_matrices(scene.camera, 320, 240)
+    rg = b2rt.RayGen(1 << 21, ctx)
+    prim = b2rt.RayBuffer()
+    rg.primary(prim, origin, m, 320, 240, scene.camera["far"])
+    tracer.traceBatch(prim)
+    sec = b2rt.RayBuffer()
+    rg.ao(sec, prim, scene, 2, scene.camera["far"], True)
+    sec.setNeedClosestHit(True)
+    out = []
+    try:
+        for variant in pair:
+            ctx.set_trace_config(variant=variant)
+            per = []
+            for rb in (prim, sec):
+                tracer.traceBatch(rb)
+                per.append(rb.getResults().copy())
+            out.append(per)
+    finally:
+        ctx.set_trace_config()
+    for a, b in zip(out[0], out[1]):
+        same = a["id"] == b["id"]
+        assert same.mean() >= ID_AGREE
+        assert a[same].tobytes() == b[same].tobytes()
+        assert (a["t"][~same] == b["t"][~same]).all()
