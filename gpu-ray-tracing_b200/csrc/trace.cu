@@ -594,17 +594,20 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     }
     int variant = ctx->cfg.variant;
     if (variant < 0) {
-        // measured on B200 (profiles/r01_explore_*_v2.log): one 1024-thread CTA per SM with a 2048-node shared top of
-        // the tree wins on frame-sized batches (shorter tail, more node visits served from shared memory); four
-        // 256-thread CTAs win on multi-million-ray batches
-        variant = (numRays <= (4 << 20)) ? 8 : 1;
-        // any-hit batches share subtrees inside a CTA once the pool is dry; two 512-thread CTAs per SM measured best
-        // on C3's 2 Mi-ray AO batches (2 780 vs 2 710 Mrays/s for variant 6, 2 750 for variant 1)
-        if ((flags & B2RT_TRACE_ANY_HIT) && numRays <= (4 << 20)) variant = 9;
-        // a BVH several times the size of L2 (126 MB): most node visits go to DRAM, and the 8-wide compressed private form
-        // (80 bytes per 8 children instead of 64 per 2, trace_wide.cu) wins -- C4, 1.2 GB of Compact2 arrays: 500 vs 425
-        // Mrays/s.  It is built on first use (host collapse of the private copy, api.cu:ensureWide).
-        if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 104;
+        // measured on B200 (profiles/r01_explore_*.log): one 1024-thread CTA per SM with a 2048-node shared top of the
+        // tree and the look-ahead leaf loop wins on frame-sized batches (shorter tail, more node visits served from shared
+        // memory); any-hit batches share subtrees inside a CTA once the pool is dry, two 512-thread CTAs per SM measured best
+        // on C3's 2 Mi-ray AO batches
+        variant = (flags & B2RT_TRACE_ANY_HIT) ? 9 : 8;
+        if (numRays > (4 << 20)) {
+            // multi-million-ray batches: four 256-thread CTAs per SM beat the big CTA (C5: 3 020 vs 2 830 Mrays/s), and for
+            // closest-hit rays the 8-wide compressed private form (trace_wide.cu; built on first use, api.cu:ensureWide) with
+            // its look-ahead triangle loop beats both (3 240)
+            variant = (flags & B2RT_TRACE_ANY_HIT) ? 1 : 106;
+        }
+        // a BVH several times the size of L2 (126 MB): most node visits go to DRAM, and the 8-wide form (80 bytes per 8
+        // children instead of 64 per 2) wins at every batch size -- C4, 1.2 GB of Compact2 arrays: 566 vs 425 Mrays/s
+        if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 106;
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {

@@ -46,7 +46,7 @@ __device__ __forceinline__ float byteToUnitFloat(unsigned word, unsigned one)
     return __uint_as_float(r);
 }
 
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
     const int lane = threadIdx.x & 31;
@@ -172,6 +172,39 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             // hold triangles, intersecting now would run the Woop test at a few lanes wide (ncu: 3.6 active threads per
             // triangle-loop instruction without it) -- park the group on the stack and keep traversing instead.
             const int lanesHere = __popc(__activemask());
+            if (LEAF == 1) {
+                // as trace.cu LEAF == 1: row 0 of the NEXT triangle of the group is requested before the current one is tested
+                // (the hit mask names it), Woop test without early-outs -- the same operations in the same order
+                int tri = (int)T.x + (T.y ? __ffs(T.y) - 1 : 0);
+                float4 v00 = ldg4(p.woop + (size_t)tri * 3);
+                while (T.y != 0u) {
+                    if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < kWideStack - 2) {
+                        stack[sp++] = T;
+                        break;
+                    }
+                    if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
+                    T.y &= T.y - 1u;
+                    const int ntri = (int)T.x + (T.y ? __ffs(T.y) - 1 : 0);
+                    const float4* w = p.woop + (size_t)tri * 3;
+                    const float4 n00 = ldg4(p.woop + (size_t)ntri * 3);
+                    const float4 v11 = ldg4(w + 1), v22 = ldg4(w + 2);
+                    const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
+                    const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
+                    const float t = __fmul_rn(Oz, invDz);
+                    const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
+                    const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
+                    const float u = __fmaf_rn(t, Dx, Ox);
+                    const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
+                    const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
+                    const float v = __fmaf_rn(t, Dy, Oy);
+                    if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                        hitT = t; hitIndex = tri;
+                        if (BARY) { hitU = u; hitV = v; }
+                        if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; }
+                    }
+                    v00 = n00; tri = ntri;
+                }
+            } else
             while (T.y != 0u) {
                 if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < kWideStack - 2) {
                     stack[sp++] = T;
@@ -232,10 +265,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>;
     int blocksPerSm = 0;
     B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, 0));
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
@@ -251,18 +284,18 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int BLOCK, int MIN_BLOCKS, int POSTPONE>
+template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0>
 static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS)
-        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream)
-                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream);
-    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream)
-                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream);
-    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream)
-                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE>(ctx, p, stream);
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream);
 }
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
@@ -290,6 +323,8 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     case 103: return launchWideFlags<256, 4, 5>(ctx, p, flags, stream);   // <= 64 regs, postpone below 1/5
     case 104: return launchWideFlags<256, 4, 3>(ctx, p, flags, stream);   // postpone below 1/3
     case 105: return launchWideFlags<256, 4, 2>(ctx, p, flags, stream);   // postpone below 1/2
+    case 106: return launchWideFlags<256, 4, 3, 1>(ctx, p, flags, stream);  // 104 with the look-ahead triangle loop
+    case 107: return launchWideFlags<256, 4, 0, 1>(ctx, p, flags, stream);  // 102 with the look-ahead triangle loop
     }
 }
 
