@@ -603,11 +603,11 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
             // multi-million-ray batches: four 256-thread CTAs per SM beat the big CTA (C5: 3 020 vs 2 830 Mrays/s), and for
             // closest-hit rays the 8-wide compressed private form (trace_wide.cu; built on first use, api.cu:ensureWide) with
             // its look-ahead triangle loop beats both (3 240)
-            variant = (flags & B2RT_TRACE_ANY_HIT) ? 1 : 106;
+            variant = (flags & B2RT_TRACE_ANY_HIT) ? 1 : 108;
         }
         // a BVH several times the size of L2 (126 MB): most node visits go to DRAM, and the 8-wide form (80 bytes per 8
         // children instead of 64 per 2) wins at every batch size -- C4, 1.2 GB of Compact2 arrays: 566 vs 425 Mrays/s
-        if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 106;
+        if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 108;
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {

@@ -46,11 +46,24 @@ __device__ __forceinline__ float byteToUnitFloat(unsigned word, unsigned one)
     return __uint_as_float(r);
 }
 
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
     const int lane = threadIdx.x & 31;
-    uint2 stack[kWideStack];
+    // Traversal stack: the first SSLOTS entries in shared memory (slot k of this thread at s_stack[k * BLOCK]: consecutive
+    // threads, consecutive 8-byte words), the rest in local memory.  Entirely in local memory (SSLOTS == 0) the stack moved
+    // 23 GB through L1 per 64 Mi-ray launch and its pops held 6 % of the stall samples (ncu source page, C5).
+    extern __shared__ uint2 s_wideStack[];
+    uint2* s_stack = s_wideStack + threadIdx.x;
+    uint2 lstack[kWideStack];
+    auto push = [&](int& sp_, const uint2 v) {
+        if (sp_ < SSLOTS) s_stack[sp_ * BLOCK] = v; else lstack[sp_ - SSLOTS] = v;
+        sp_++;
+    };
+    auto pop = [&](int& sp_) -> uint2 {
+        sp_--;
+        return (sp_ < SSLOTS) ? s_stack[sp_ * BLOCK] : lstack[sp_ - SSLOTS];
+    };
     const unsigned one = p.one;                         // 0x3F800000 from the parameter block: opaque to ptxas (see byteToUnitFloat)
 
     float origx = 0, origy = 0, origz = 0, dirx = 0, diry = 0, dirz = 0;
@@ -114,7 +127,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 if (STATS) { const unsigned am = __activemask(); stNodeLanes++; if (lane == __ffs(am) - 1) stNodeIters++; }
                 const unsigned bit = 31u - __clz(G.y);
                 G.y &= ~(1u << bit);
-                if (G.y > 0x00FFFFFFu) stack[sp++] = G;
+                if (G.y > 0x00FFFFFFu) push(sp, G);
                 const unsigned slot = (bit - 24u) ^ (octinv4 & 7u);
                 const unsigned rel = __popc(G.y & ((1u << slot) - 1u) & 0xFFu);
                 const float4* n = p.nodes + (size_t)(G.x + rel) * 5;
@@ -179,7 +192,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 float4 v00 = ldg4(p.woop + (size_t)tri * 3);
                 while (T.y != 0u) {
                     if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < kWideStack - 2) {
-                        stack[sp++] = T;
+                        push(sp, T);
                         break;
                     }
                     if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
@@ -207,7 +220,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             } else
             while (T.y != 0u) {
                 if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < kWideStack - 2) {
-                    stack[sp++] = T;
+                    push(sp, T);
                     break;
                 }
                 if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
@@ -240,7 +253,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             // ---- next group ---------------------------------------------------------------------
             if (G.y <= 0x00FFFFFFu) {
                 if (sp == 0) { active = false; break; }
-                G = stack[--sp];
+                G = pop(sp);
             }
             if (__popc(__activemask()) < threshold) break;          // dynamic fetch: refill the idle lanes
         }
@@ -265,12 +278,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>;
     int blocksPerSm = 0;
-    B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, 0));
+    const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2);
+    B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, smem));
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
     long long grid = (long long)ctx->smCount * blocksPerSm;
@@ -279,23 +294,23 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     if (grid < 1) grid = 1;
     p.warpCounter = ctx->warpCounter + (ctx->launchSlot++ % b2rt_ctx::kLaunchSlots) * 32;
     B2RT_CUDA(ctx, cudaMemsetAsync(p.warpCounter, 0, sizeof(int), stream));
-    kern<<<(unsigned)grid, BLOCK, 0, stream>>>(p);
+    kern<<<(unsigned)grid, BLOCK, smem, stream>>>(p);
     B2RT_CHECK_LAUNCH(ctx, "traceWideKernel");
     return B2RT_OK;
 }
 
-template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0>
+template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0>
 static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS)
-        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream)
-                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream);
-    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream)
-                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream);
-    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream)
-                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF>(ctx, p, stream);
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
 }
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
@@ -325,6 +340,9 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     case 105: return launchWideFlags<256, 4, 2>(ctx, p, flags, stream);   // postpone below 1/2
     case 106: return launchWideFlags<256, 4, 3, 1>(ctx, p, flags, stream);  // 104 with the look-ahead triangle loop
     case 107: return launchWideFlags<256, 4, 0, 1>(ctx, p, flags, stream);  // 102 with the look-ahead triangle loop
+    case 108: return launchWideFlags<256, 4, 3, 1, 8>(ctx, p, flags, stream);   // 106 with 8 stack entries in shared memory
+    case 109: return launchWideFlags<256, 4, 3, 1, 12>(ctx, p, flags, stream);  // 106 with 12
+    case 110: return launchWideFlags<256, 4, 3, 1, 4>(ctx, p, flags, stream);   // 106 with 4
     }
 }
 
