@@ -418,6 +418,10 @@ def product_arm(args):
     # the BVH arrays once per step (L2 is flushed between steps) -- against the ncu-measured DRAM traffic of the launch
     bvh_bytes = float(arrays["nodes"].nbytes + arrays["woop"].nbytes + arrays["triIndex"].nbytes)
     compulsory = (launched / n_launch_step) * (32 + 8) + bvh_bytes / n_launch_step
+    # which kernel the library's default policy launches for these batches (trace.cu:launchTrace)
+    wide = (args.variant >= 100) or (args.variant < 0 and (
+        max(b.getSize() for b, _ in frame.batches) > (4 << 20) or
+        float(arrays["nodes"].nbytes + arrays["woop"].nbytes) > 2 * 126e6))
     sm_hz = (sampler.summary()["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)) * 1e6
     sm_count = ctx.sm_count()
     fp32_rate = fp32_all / ws / (ms_total_max / args.steps * 1e-3)
@@ -437,7 +441,7 @@ def product_arm(args):
         "wall_s_timed_region": t_wall,
         "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
-                     "traffic": traffic, "peak_source": peak_src, "kernel": "traceKernel",
+                     "traffic": traffic, "peak_source": peak_src, "kernel": "traceWideKernel" if wide else "traceKernel",
                      "algorithmic_bytes_per_launch": bytes_all / ws / n_launch_step, "avg_launch_ms": avg_launch_ms,
                      "compulsory": {"bytes_per_launch": compulsory, "achieved": compulsory / (avg_launch_ms * 1e-3) * 1e-9,
                                     "frac": compulsory / (avg_launch_ms * 1e-3) * 1e-9 / peak_gbs,
