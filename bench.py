@@ -419,9 +419,7 @@ def product_arm(args):
     bvh_bytes = float(arrays["nodes"].nbytes + arrays["woop"].nbytes + arrays["triIndex"].nbytes)
     compulsory = (launched / n_launch_step) * (32 + 8) + bvh_bytes / n_launch_step
     # which kernel the library's default policy launches for these batches (trace.cu:launchTrace)
-    wide = (args.variant >= 100) or (args.variant < 0 and (
-        max(b.getSize() for b, _ in frame.batches) > (4 << 20) or
-        float(arrays["nodes"].nbytes + arrays["woop"].nbytes) > 2 * 126e6))
+    wide = (args.variant >= 100) or (args.variant < 0 and float(arrays["nodes"].nbytes + arrays["woop"].nbytes) > float(48 << 20))
     sm_hz = (sampler.summary()["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)) * 1e6
     sm_count = ctx.sm_count()
     fp32_rate = fp32_all / ws / (ms_total_max / args.steps * 1e-3)

@@ -594,20 +594,18 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     }
     int variant = ctx->cfg.variant;
     if (variant < 0) {
-        // measured on B200 (profiles/r01_explore_*.log): one 1024-thread CTA per SM with a 2048-node shared top of the
-        // tree and the look-ahead leaf loop wins on frame-sized batches (shorter tail, more node visits served from shared
-        // memory); any-hit batches share subtrees inside a CTA once the pool is dry, two 512-thread CTAs per SM measured best
-        // on C3's 2 Mi-ray AO batches
+        // Measured on B200 (profiles/r01_explore_*_final.log, r01_explore_c{2,3,5}_wide_policy.log).  Binary kernel: one
+        // 1024-thread CTA per SM with a 2048-node shared top of the tree and the look-ahead leaf loop wins on frame-sized
+        // batches (shorter tail, more node visits served from shared memory); any-hit batches share subtrees inside a CTA
+        // once the pool is dry, two 512-thread CTAs per SM; four 256-thread CTAs per SM on multi-million-ray batches.
         variant = (flags & B2RT_TRACE_ANY_HIT) ? 9 : 8;
-        if (numRays > (4 << 20)) {
-            // multi-million-ray batches: four 256-thread CTAs per SM beat the big CTA (C5: 3 020 vs 2 830 Mrays/s), and for
-            // closest-hit rays the 8-wide compressed private form (trace_wide.cu; built on first use, api.cu:ensureWide) with
-            // its look-ahead triangle loop beats both (3 240)
-            variant = (flags & B2RT_TRACE_ANY_HIT) ? 1 : 108;
-        }
-        // a BVH several times the size of L2 (126 MB): most node visits go to DRAM, and the 8-wide form (80 bytes per 8
-        // children instead of 64 per 2) wins at every batch size -- C4, 1.2 GB of Compact2 arrays: 566 vs 425 Mrays/s
-        if (ctx->nodeBytes + ctx->woopBytes > 2 * ctx->l2Bytes) variant = 108;
+        if (numRays > (4 << 20)) variant = 1;
+        // The 8-wide compressed private form (trace_wide.cu; built on first use, api.cu:ensureWide) wins once the BVH is
+        // large against what an SM keeps close -- 80 bytes per 8 children instead of 64 per 2, fewer dependent fetches per
+        // ray: knot 910 K triangles (70 MB of nodes + Woop rows): AO any-hit 3 100 vs 2 900, 64 Mi diffuse rays 3 210 vs
+        // 3 020; strands 6.5 M triangles (1.2 GB): 574 vs 425.  On the 351 K-triangle interior (32 MB) the binary kernel
+        // keeps a 25 % lead (4 800 vs 3 780), so the switch is the size of the two arrays.
+        if (ctx->nodeBytes + ctx->woopBytes > (size_t(48) << 20)) variant = 108;
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {

@@ -343,6 +343,9 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     case 108: return launchWideFlags<256, 4, 3, 1, 8>(ctx, p, flags, stream);   // 106 with 8 stack entries in shared memory
     case 109: return launchWideFlags<256, 4, 3, 1, 12>(ctx, p, flags, stream);  // 106 with 12
     case 110: return launchWideFlags<256, 4, 3, 1, 4>(ctx, p, flags, stream);   // 106 with 4
+    case 111: return launchWideFlags<256, 4, 0, 1, 8>(ctx, p, flags, stream);   // 108 without postponing
+    case 112: return launchWideFlags<256, 4, 2, 1, 8>(ctx, p, flags, stream);   // 108, postpone below 1/2
+    case 113: return launchWideFlags<512, 2, 3, 1, 8>(ctx, p, flags, stream);   // 108 in two 512-thread CTAs
     }
 }
 
