@@ -113,7 +113,8 @@ __device__ __forceinline__ u64 keyPrefix(u64 mid, u64 hi, int shift, int passes)
 template <bool AOS>
 __global__ void __launch_bounds__(256) mortonKeysKernel(const float4* __restrict__ rays, int n, const unsigned* box,
                                                         const float* boxF, u64* lo, u64* mid, u64* hi, u64* prefix,
-                                                        unsigned* slots, MortonKey* keysAos, int prefixShift, int prefixBytes)
+                                                        unsigned* slots, MortonKey* keysAos, int prefixShift, int prefixBytes,
+                                                        float4* rayCopy, const int32_t* slotToID, int32_t* slotToIDCopy)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -146,6 +147,10 @@ __global__ void __launch_bounds__(256) mortonKeysKernel(const float4* __restrict
         lo[i] = (u64)hash[0] | ((u64)hash[1] << 32);
         mid[i] = (u64)hash[2] | ((u64)hash[3] << 32);
         hi[i] = (u64)hash[4] | ((u64)hash[5] << 32);
+        // the sort is in place: the gather at its end reads these copies (made here, where the rays pass through registers
+        // anyway, instead of by two device-to-device copies afterwards)
+        rayCopy[2 * (size_t)i] = o; rayCopy[2 * (size_t)i + 1] = d;
+        slotToIDCopy[i] = slotToID[i];
         prefix[i] = keyPrefix((u64)hash[2] | ((u64)hash[3] << 32), (u64)hash[4] | ((u64)hash[5] << 32), prefixShift, prefixBytes);
         slots[i] = (unsigned)i;
     }
@@ -449,7 +454,8 @@ int b2rt_morton_keys(b2rt_ctx* ctx, const void* rays, int64_t n, const float aab
     float* boxF = ctx->aabbDev;     // 8 floats allocated; reuse as float box
     B2RT_CUDA(ctx, cudaMemcpyAsync(boxF, aabb, 6 * sizeof(float), cudaMemcpyHostToDevice, s));
     mortonKeysKernel<true><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(static_cast<const float4*>(rays), (int)n, nullptr, boxF,
-                                                                      nullptr, nullptr, nullptr, nullptr, nullptr, static_cast<MortonKey*>(keys), 0, 0);
+                                                                      nullptr, nullptr, nullptr, nullptr, nullptr, static_cast<MortonKey*>(keys), 0, 0,
+                                                                      nullptr, nullptr, nullptr);
     B2RT_CHECK_LAUNCH(ctx, "mortonKeysKernel");
     B2RT_CUDA(ctx, cudaStreamSynchronize(s));   // aabb is a host pointer the caller may reuse
     return B2RT_OK;
@@ -497,7 +503,7 @@ int b2rt_morton_sort(b2rt_ctx* ctx, void* rays, int32_t* idToSlot, int32_t* slot
     const int prefixShift = ctx->sortMode >= 64 ? ctx->sortMode : kPrefixShiftDefault;
     const int passesA = prefixPasses(prefixShift);
     mortonKeysKernel<false><<<g, 256, 0, s>>>(static_cast<const float4*>(rays), n, reinterpret_cast<unsigned*>(ctx->aabbDev), nullptr,
-                                             wLo, wMid, wHi, kA, sA, nullptr, prefixShift, passesA);
+                                             wLo, wMid, wHi, kA, sA, nullptr, prefixShift, passesA, oldRays, slotToID, oldSlotToID);
     B2RT_CHECK_LAUNCH(ctx, "mortonKeysKernel");
 
     unsigned* slotsCur = sA; unsigned* slotsAlt = sB;
@@ -556,8 +562,6 @@ int b2rt_morton_sort(b2rt_ctx* ctx, void* rays, int32_t* idToSlot, int32_t* slot
         }
     }
 
-    B2RT_CUDA(ctx, cudaMemcpyAsync(oldRays, rays, (size_t)n * 32, cudaMemcpyDeviceToDevice, s));
-    B2RT_CUDA(ctx, cudaMemcpyAsync(oldSlotToID, slotToID, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
     reorderRaysKernel<<<g, 256, 0, s>>>(slotsCur, oldRays, oldSlotToID, static_cast<float4*>(rays), idToSlot, slotToID, n, 1);
     B2RT_CHECK_LAUNCH(ctx, "reorderRaysKernel");
     if (aabbOut) return readAABB(ctx, aabbOut, s);
