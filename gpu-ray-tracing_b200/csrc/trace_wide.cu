@@ -325,7 +325,10 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     p.woop = ctx->wideWoop;
     p.triIndex = ctx->wideTriIndex;
     p.numRays = (int)numRays;
-    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
+    // refill below 24 live lanes (the binary kernel and the reference use 20): a wide step is ~3x as many instructions as a
+    // binary one, so an idle lane costs more; measured 12 / 16 / 20 / 24 / 28 on C5: 3 119 / 3 205 / 3 203 / 3 241 / 3 175,
+    // C3: 3 086 (20) -> 3 153 (24)  (profiles/r01_explore_c{3,5}_wide_threshold.log)
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 24 : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
