@@ -171,13 +171,20 @@ __global__ void __launch_bounds__(kRsThreads) rsHistKernel(const u64* __restrict
     __syncthreads();
     const long long base = (long long)blockIdx.x * kRsTile;
     u64 ored = 0;
-#pragma unroll 4
+    // all 16 loads of the thread first (independent, in flight together), then the counting: with the loads issued four at a
+    // time the kernel was latency-bound, 11 us for 16 MB
+    u64 k[kRsItems];
+#pragma unroll
+    for (int j = 0; j < kRsItems; j++) {
+        const long long i = base + j * kRsThreads + threadIdx.x;
+        k[j] = (i < n) ? keys[i] : 0ull;
+    }
+#pragma unroll
     for (int j = 0; j < kRsItems; j++) {
         const long long i = base + j * kRsThreads + threadIdx.x;
         if (i < n) {
-            const u64 k = keys[i];
-            ored |= k;
-            atomicAdd(&hist[(unsigned)(k >> shift) & 0xffu], 1u);
+            ored |= k[j];
+            atomicAdd(&hist[(unsigned)(k[j] >> shift) & 0xffu], 1u);
         }
     }
     __syncthreads();
