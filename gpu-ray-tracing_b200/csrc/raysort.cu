@@ -157,10 +157,13 @@ __global__ void __launch_bounds__(256) mortonKeysKernel(const float4* __restrict
 }
 
 // ---- radix sort ------------------------------------------------------------------------------
-constexpr int kRsThreads = 256, kRsItems = 16, kRsTile = kRsThreads * kRsItems, kRsBins = 256;    // histogram kernel
+// 2 048-key tiles (256 threads x 8 keys in both kernels).  4 096-key tiles on 512 scatter threads were 4 % slower end to end: at 64
+// registers an SM holds 1 024 scatter threads either way, but small blocks refill one at a time as they finish, so the partial
+// last wave costs a short tile, not a long one (1 536-key tiles: slower again, the per-digit write runs get too short).
+constexpr int kRsThreads = 256, kRsItems = 8, kRsTile = kRsThreads * kRsItems, kRsBins = 256;    // histogram kernel
 // scatter kernel: the same 4 096-key tile over 512 threads x 8 keys -- its ranking loops are chains of match / shared-memory
 // steps, so half as many steps per thread and twice the warps per tile
-constexpr int kScThreads = 512, kScItems = kRsTile / kScThreads, kScWarps = kScThreads / 32, kScWarpTile = kRsTile / kScWarps;
+constexpr int kScThreads = 256, kScItems = kRsTile / kScThreads, kScWarps = kScThreads / 32, kScWarpTile = kRsTile / kScWarps;
 
 // blockHist layout: [bin][block]
 __global__ void __launch_bounds__(kRsThreads) rsHistKernel(const u64* __restrict__ keys, int n, int shift,
