@@ -161,8 +161,7 @@ __global__ void __launch_bounds__(256) mortonKeysKernel(const float4* __restrict
 // registers an SM holds 1 024 scatter threads either way, but small blocks refill one at a time as they finish, so the partial
 // last wave costs a short tile, not a long one (1 536-key tiles: slower again, the per-digit write runs get too short).
 constexpr int kRsThreads = 256, kRsItems = 8, kRsTile = kRsThreads * kRsItems, kRsBins = 256;    // histogram kernel
-// scatter kernel: the same 4 096-key tile over 512 threads x 8 keys -- its ranking loops are chains of match / shared-memory
-// steps, so half as many steps per thread and twice the warps per tile
+// scatter kernel: the same tile, 8 keys per thread
 constexpr int kScThreads = 256, kScItems = kRsTile / kScThreads, kScWarps = kScThreads / 32, kScWarpTile = kRsTile / kScWarps;
 
 // blockHist layout: [bin][block]
@@ -232,8 +231,8 @@ __global__ void __launch_bounds__(512) rsScanKernel(unsigned* blockHist, int num
 
 // Stable scatter of one tile.  The tile is first put in digit order in shared memory (rank = start of the digit inside the
 // tile + same-digit items of earlier warps + same-digit items earlier in this warp), then written out linearly: consecutive
-// threads write consecutive elements of a digit's run, so the global stores are whole lines (4 096 items over 256 digits =
-// runs of 16 keys = 128 B) instead of one 32-byte sector per key.  (Scattering straight from registers ran at 0.96 TB/s
+// threads write consecutive elements of a digit's run, so the global stores are whole lines (2 048 items over 256 digits =
+// runs of 8 keys = 64 B on average, two sectors) instead of one 32-byte sector per key.  (Scattering straight from registers ran at 0.96 TB/s
 // of useful traffic, 50 us per pass on 2 Mi keys.)
 // Lanes of the warp holding the same digit as this one, from nine ballots (one per digit bit + validity).  match.any does
 // the same in one instruction but at a fraction of the throughput: with it the ranking loops were most of a pass.
@@ -258,7 +257,7 @@ __global__ void __launch_bounds__(kScThreads) rsScatterKernel(const u64* __restr
     __shared__ unsigned warpHist[kScWarps][kRsBins];
     __shared__ unsigned globalBase[kRsBins];            // destination of the digit's first item of this tile, minus its place in the tile
     __shared__ unsigned scanTmp[8];
-    extern __shared__ u64 s_tile[];                     // kRsTile keys, then kRsTile slots (48 KB, opted in by the launcher)
+    extern __shared__ u64 s_tile[];                     // kRsTile keys, then kRsTile slots (24 KB)
     u64* sKey = s_tile;
     unsigned* sSlot = reinterpret_cast<unsigned*>(s_tile + kRsTile);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
