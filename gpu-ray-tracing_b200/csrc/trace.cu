@@ -67,24 +67,7 @@ constexpr int kShareRounds = 4;     // stack entries a lane may hand over per vi
 constexpr int kShareQueue = 128;    // queue entries (int4: ray, stack entry, hit distance); 2 KB keeps the L1 carve-out where it was
 constexpr int kShareList = 1024;    // shared rays per CTA (global memory, one slice per CTA and launch slot)
 
-// MIG (MODE bit 1, closest-hit kernels): whole-RAY migration in the tail of a launch.  Once the work counter has run dry a
-// launch is a handful of warps, each alternating between node and leaf loops for its few live lanes: lanes that are out of
-// phase ADD their steps (the last warp of a C2 primary launch runs 272 node + 48 triangle iterations after its last fetch while
-// its longest ray needs 162), and every step of such a warp is a ~250 ns dependent chain.  So a warp that comes back to the top
-// of the loop with two or more live rays while other warps of the CTA are idle puts all but one of them -- hit so far, node /
-// leaf / stack state, the <= STACK_SMEM stack entries -- into a mailbox in shared memory, and idle warps take ONE ray each
-// and run it alone.  A ray has one owner at any time and is traversed with the same arithmetic in the same order wherever it
-// runs, so results do not change.  Try-lock only; idle warps poll until the mailbox is empty and every warp is idle.
-struct MigArea {
-    int lock;               // 0 free, 1 taken
-    int count;              // rays in the mailbox (used as a stack); changed under the lock
-    int idleWarps;          // warps without a ray in flight (includes warps that have left)
-    int pad;
-};
-constexpr int kMigSlots = 32;       // rays the mailbox holds
-constexpr int kMigWords = 32;       // words per ray: 0 ray, 1 hitIndex, 2 nodeAddr, 3 leafAddr, 4 tos, 5 sp, 6 hitT, 7 hitU, 8 hitV, 12.. stack
-
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int MODE>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
     extern __shared__ float4 s_dyn[];
@@ -117,17 +100,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
     }
     // SHARE: [ShareArea][queue] behind the planes
     constexpr bool SHARE = ANY_HIT;
-    constexpr int LEAF = MODE & 1;
-    constexpr bool MIG = (MODE & 2) != 0 && !ANY_HIT;     // whole-ray migration in the tail (closest-hit kernels)
     constexpr int kQueue = kShareQueue, kListCap = kShareList, kWarps = BLOCK / 32;
     ShareArea* s_share = reinterpret_cast<ShareArea*>(reinterpret_cast<char*>(s_plane) + (size_t)topNodes * 56);
     int4* s_queue = reinterpret_cast<int4*>(s_share + 1);
     int* s_list = p.shareList + (size_t)blockIdx.x * kListCap;
     if (SHARE && threadIdx.x == 0) { s_share->lock = 0; s_share->head = 0; s_share->tail = 0; s_share->idleWarps = 0; s_share->listCount = 0; }
-    // MIG: [MigArea][mailbox] in the same place (the closest-hit kernels have no sharing queue)
-    MigArea* s_mig = reinterpret_cast<MigArea*>(s_share);
-    int* s_mail = reinterpret_cast<int*>(s_mig + 1);
-    if (MIG && threadIdx.x == 0) { s_mig->lock = 0; s_mig->count = 0; s_mig->idleWarps = 0; }
     __syncthreads();
     unsigned sTop = (unsigned)__cvta_generic_to_shared(s_plane);              // 32-bit shared address of plane 0
     asm volatile("mov.u32 %0, %0;" : "+r"(sTop));      // opaque: keep it in a register instead of re-deriving it per node
@@ -188,9 +165,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
         // A warp of this CTA without work means the pool is empty: start visiting the queue.  poolEmpty has to stay
         // warp-uniform (it guards full-mask shuffles) and the lanes need not have reconverged after the stores above, so
         // they could see different values of the counter: lane 0 reads, everybody takes its answer.
-        if ((SHARE || MIG) && !poolEmpty) {
+        if (SHARE && !poolEmpty) {
             int idle = 0;
-            if (lane == 0) idle = SHARE ? *reinterpret_cast<volatile int*>(&s_share->idleWarps) : *reinterpret_cast<volatile int*>(&s_mig->idleWarps);
+            if (lane == 0) idle = *reinterpret_cast<volatile int*>(&s_share->idleWarps);
             if (__shfl_sync(kFull, idle, 0) > 0) poolEmpty = true;
         }
         if (maskT != 0 && !poolEmpty) {
@@ -336,91 +313,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             }
             if (leave) break;
         }
-        if (MIG && poolEmpty) {
-            static_assert(!MIG || (STACK_SMEM >= 1 && 12 + STACK_SMEM <= kMigWords), "a ray's shared stack slots fit its mailbox entry");
-            bool leave = false;
-            volatile MigArea* mg = s_mig;
-            for (;;) {
-                const bool busy = (nodeAddr != kSentinel);
-                const unsigned busyMask = __ballot_sync(kFull, busy);
-                const int nBusy = __popc(busyMask);
-                // hints read by lane 0 for the whole warp (every decision below is warp-uniform); exact values under the lock
-                int cnt = 0, idleW = 0;
-                if (lane == 0) { cnt = mg->count; idleW = mg->idleWarps; }
-                cnt = __shfl_sync(kFull, cnt, 0); idleW = __shfl_sync(kFull, idleW, 0);
-                const bool wantPop = nBusy == 0 && cnt > 0;
-                const bool wantPush = nBusy >= 2 && idleW > 0 && cnt < kMigSlots / 2;
-                if (wantPop || wantPush) {
-                    int got = 0;
-                    if (lane == 0) got = (atomicCAS(&s_mig->lock, 0, 1) == 0);
-                    got = __shfl_sync(kFull, got, 0);
-                    if (got) {
-                        __threadfence_block();
-                        if (lane == 0) cnt = mg->count;
-                        cnt = __shfl_sync(kFull, cnt, 0);
-                        if (wantPush) {
-                            // every live ray but the first, as long as its stack has not spilled to local memory
-                            const bool cand = busy && lane != __ffs(busyMask) - 1 && sp <= STACK_SMEM;
-                            const unsigned candMask = __ballot_sync(kFull, cand);
-                            const int nGive = min(__popc(candMask), min(idleW, kMigSlots - cnt));
-                            const int rank = __popc(candMask & ((1u << lane) - 1u));
-                            if (cand && rank < nGive) {
-                                int* m = s_mail + (cnt + rank) * kMigWords;
-                                m[0] = rayidx; m[1] = hitIndex; m[2] = nodeAddr; m[3] = leafAddr; m[4] = tos; m[5] = sp;
-                                m[6] = __float_as_int(hitT); m[7] = __float_as_int(hitU); m[8] = __float_as_int(hitV);
-                                for (int k = 0; k < sp; k++) m[12 + k] = s_stack[k * BLOCK];
-                                rayidx = -1; nodeAddr = kSentinel;          // handed over: nothing to store here
-                                if (STATS) stShares++;
-                            }
-                            cnt += max(nGive, 0);
-                        } else if (cnt > 0) {
-                            // the whole warp is idle: lane 0 takes one ray and runs it alone
-                            cnt--;
-                            if (lane == 0) {
-                                const int* m = s_mail + cnt * kMigWords;
-                                rayidx = m[0]; hitIndex = m[1]; nodeAddr = m[2]; leafAddr = m[3]; tos = m[4]; sp = m[5];
-                                hitT = __int_as_float(m[6]); hitU = __int_as_float(m[7]); hitV = __int_as_float(m[8]);
-                                for (int k = 0; k < sp; k++) s_stack[k * BLOCK] = m[12 + k];
-                                const float4 o = ldg4(p.rays + 2 * (size_t)rayidx);
-                                const float4 d = ldg4(p.rays + 2 * (size_t)rayidx + 1);
-                                origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
-                                dirx = d.x; diry = d.y; dirz = d.z;
-                                const float ooeps = 8.271806125530277e-25f;
-                                idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-                                idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-                                idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-                                oodx = origx * idirx; oody = origy * idiry; oodz = origz * idirz;
-                                if (countedIdle) atomicSub(&s_mig->idleWarps, 1);
-                            }
-                            countedIdle = false;
-                        }
-                        __syncwarp();
-                        if (lane == 0) {
-                            mg->count = cnt;
-                            __threadfence_block();
-                            atomicExch(&s_mig->lock, 0);
-                        }
-                    }
-                }
-                if (__ballot_sync(kFull, nodeAddr != kSentinel) != 0) break;        // somebody has work: traverse
-                // the whole warp is idle: say so, then wait for rays or for everybody else to run dry as well
-                if (!countedIdle) {
-                    if (lane == 0) atomicAdd(&s_mig->idleWarps, 1);
-                    countedIdle = true;
-                }
-                {
-                    int done = 0;
-                    if (lane == 0) done = (mg->count <= 0 && mg->idleWarps >= kWarps);
-                    if (__shfl_sync(kFull, done, 0)) { leave = true; break; }
-                }
-                __nanosleep(100);
-            }
-            if (leave) break;
-        }
-        if ((!SHARE && !MIG) || !poolEmpty) { if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break; }     // warp out of work
+        if (!SHARE || !poolEmpty) { if (__ballot_sync(kFull, nodeAddr != kSentinel) == 0) break; }     // warp out of work
 
         // after the pool is empty: without SHARE never leave the loop early; with SHARE come back up after every pass
-        const int threshold = poolEmpty ? ((SHARE || MIG) ? 33 : 0) : p.fetchThreshold;
+        const int threshold = poolEmpty ? (SHARE ? 33 : 0) : p.fetchThreshold;
 
         // ---- traversal --------------------------------------------------------------------
         while (nodeAddr != kSentinel) {
@@ -542,7 +438,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             // dynamic fetch: too few lanes left -> leave and refill the idle ones
             if (__popc(__activemask()) < threshold) break;
             if (SHARE && !poolEmpty && *reinterpret_cast<volatile int*>(&s_share->idleWarps) > 0) break;
-            if (MIG && !poolEmpty && *reinterpret_cast<volatile int*>(&s_mig->idleWarps) > 0) break;
         }
     }
 
@@ -613,17 +508,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 // ---------------------------------------------------------------------------------------------
 struct Variant { int block; int stackSmem; int minBlocks; };
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int MODE>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF>
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
-    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>;
+    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>;
     // any-hit kernels carry the sharing queue behind the staged nodes; the small-CTA default gives up 40 nodes for it so
     // that four CTAs still fit the 164 KB shared-memory step (the next step, 196 KB, costs 32 KB of L1)
-    constexpr bool kMig = (MODE & 2) != 0 && !ANY_HIT;
-    constexpr size_t shareBytes = ANY_HIT ? sizeof(ShareArea) + (size_t)kShareQueue * sizeof(int4)
-                                          : (kMig ? sizeof(MigArea) + (size_t)kMigSlots * kMigWords * sizeof(int) : 0);
-    // (the mailbox costs the big CTA 80 staged nodes, so that it stays inside the 164 KB shared-memory step)
-    int topNodes = ctx->cfg.top_nodes < 0 ? (BLOCK >= 1024 ? (kMig ? 1968 : 2048) : (ANY_HIT || kMig ? 432 : 512)) : ctx->cfg.top_nodes;
+    constexpr size_t shareBytes = ANY_HIT ? sizeof(ShareArea) + (size_t)kShareQueue * sizeof(int4) : 0;
+    int topNodes = ctx->cfg.top_nodes < 0 ? (BLOCK >= 1024 ? 2048 : (ANY_HIT ? 472 : 512)) : ctx->cfg.top_nodes;
     if (topNodes > ctx->topNodesAvail) topNodes = ctx->topNodesAvail;
     size_t stackBytes = (size_t)STACK_SMEM * BLOCK * sizeof(int) + shareBytes;
     // keep MIN_BLOCKS CTAs resident inside the 227 KB a CTA can opt into
@@ -657,20 +549,20 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int MODE = 0>
+template <int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF = 0>
 static int launchFlags(b2rt_ctx* ctx, TraceParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS) {
         // the instrumented build always writes barycentrics (one kernel fewer to carry)
-        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream)
-                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream);
+        return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream)
+                   : launchOne<false, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream);
     }
-    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream)
-                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream);
-    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream)
-                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, MODE>(ctx, p, stream);
+    if (any) return bary ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream)
+                         : launchOne<true, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream);
+    return bary ? launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream)
+                : launchOne<false, false, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream);
 }
 
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
@@ -727,8 +619,6 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // v6 with the look-ahead leaf loop
     case 9: return launchFlags<12, 512, 2, 1>(ctx, p, flags, stream);   // v7 with the look-ahead leaf loop
     case 10: return launchFlags<12, 256, 4, 1>(ctx, p, flags, stream);  // v1 with the look-ahead leaf loop
-    case 11: return launchFlags<12, 1024, 1, 3>(ctx, p, flags, stream); // v8 + whole-ray migration in the tail (closest hit)
-    case 12: return launchFlags<12, 512, 2, 3>(ctx, p, flags, stream);  // two 512-thread CTAs, look-ahead leaf loop, migration
     }
 }
 

@@ -348,7 +348,7 @@ def test_traces_on_two_streams_overlap_safely(b2rt, oracle, ctx):
                 assert same.mean() >= 0.999 and (got["t"][same] == want["t"][same]).all()
 
 
-@pytest.mark.parametrize("pair", [(6, 8), (1, 10), (7, 9), (8, 11), (8, 12)])
+@pytest.mark.parametrize("pair", [(6, 8), (1, 10), (7, 9)])
 def test_lookahead_leaf_loop_returns_the_same_bits(b2rt, oracle, ctx, pair):
     """LEAF = 1 (row 0 of the next triangle requested ahead, Woop test without early-outs; trace.cu) performs the same
     floating-point operations in the same order as the reference-shaped loop: wherever both kernels report the same
@@ -382,46 +382,3 @@ def test_lookahead_leaf_loop_returns_the_same_bits(b2rt, oracle, ctx, pair):
         assert same.mean() >= ID_AGREE
         assert a[same].tobytes() == b[same].tobytes()
         assert (a["t"][~same] == b["t"][~same]).all()
-
-
-@pytest.mark.parametrize("variant", [11, 12])
-@pytest.mark.parametrize("count", [1, 37, 4097, 60000])
-def test_ray_migration_in_the_tail(b2rt, oracle, ctx, variant, count):
-    """Closest-hit kernels with whole-ray migration (trace.cu MIG): once the work counter is dry, warps hand all but one of
-    their live rays to idle warps of the CTA.  Small batches run almost entirely in that mode.  A ray is traversed with the
-    same arithmetic wherever it runs: records must equal the plain kernel's bit for bit where the ids agree, ids may differ
-    only between triangles at one distance, and every ray must have been written exactly once (poisoned records)."""
-    scene = b2rt.Scene.generate("interior", 30000, 7)
-    bvh = b2rt.BVH(scene)
-    tracer = b2rt.CudaTracer(ctx)
-    tracer.writeBarycentrics = True
-    tracer.setBVH(b2rt.CudaBVH(bvh))
-    origin, m = b2rt.camera_matrices(scene.camera, 320, 240)
-    rg = b2rt.RayGen(1 << 21, ctx)
-    prim = b2rt.RayBuffer()
-    rg.primary(prim, origin, m, 320, 240, scene.camera["far"])
-    tracer.traceBatch(prim)
-    sec = b2rt.RayBuffer()
-    rg.ao(sec, prim, scene, 2, scene.camera["far"], True)
-    rays = sec.getRays().copy()
-    rays = rays[np.linspace(0, len(rays) - 1, count).astype(np.int64)].copy()
-    out = []
-    try:
-        for v in (8, variant):
-            for rep in range(3 if v == variant else 1):
-                rb = b2rt.RayBuffer()
-                rb.setRays(rays)
-                rb.setNeedClosestHit(True)
-                rb.m_results[: len(rays)].fill_(0x5A5A5A5A)
-                ctx.set_trace_config(variant=v)
-                tracer.traceBatch(rb)
-                out.append(rb.getResults().copy())
-    finally:
-        ctx.set_trace_config()
-    ref = out[0]
-    for got in out[1:]:
-        assert not (got["id"] == 0x5A5A5A5A).any(), "a ray was never written"
-        same = got["id"] == ref["id"]
-        assert same.mean() >= (ID_AGREE if count > 10000 else 0.99)
-        assert got[same].tobytes() == ref[same].tobytes()
-        assert (got["t"][~same] == ref["t"][~same]).all()
