@@ -83,9 +83,9 @@ typedef struct {
 typedef struct {
     int top_nodes;              /* nodes staged in shared memory (0 = none, -1 = default) */
     int fetch_threshold;        /* refill dead lanes when fewer than this are alive
-                                   (kepler_dynamic_fetch.cu:48 uses 20); -1 = default */
+                                   (kepler_dynamic_fetch.cu:48 uses 20); -1 = default: 20, 24 in the 8-wide kernel */
     int blocks_per_sm;          /* persistent CTAs per SM; -1 = from occupancy */
-    int variant;                /* kernel variant id; -1 = chosen from the batch size */
+    int variant;                /* kernel variant id; -1 = chosen from the batch size and the size of the BVH (trace.cu:launchTrace) */
     int l2_prefetch;            /* 1: every launch starts by pulling the private BVH arrays into L2 (bulk reads instead of
                                    cold misses on the rays' dependent chains); 0 or -1: off (no measured gain) */
 } b2rt_trace_config;
