@@ -92,9 +92,10 @@ static void relayoutNodes(const std::vector<float>& in, std::vector<float>& out,
 
 static void freeWide(b2rt_ctx* ctx)
 {
-    cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
+    cudaFree(ctx->wideNodes);                   // one allocation: nodes, Woop rows, triangle ids
     ctx->wideNodes = nullptr; ctx->wideWoop = nullptr; ctx->wideTriIndex = nullptr;
-    ctx->wideNumNodes = ctx->wideNumTris = 0;
+    ctx->wideNumNodes = ctx->wideNumTris = ctx->wideMaxDepth = 0;
+    ctx->wideBytes = 0;
     ctx->hasWide = false;
 }
 
@@ -102,7 +103,8 @@ static void freeWide(b2rt_ctx* ctx)
 // into the 8-wide compressed form.  One-off host work per BVH: D2H of the three arrays, collapse, H2D.
 int ensureWide(b2rt_ctx* ctx)
 {
-    if (ctx->hasWide) return B2RT_OK;
+    const bool greedy = (ctx->cfg.tune & B2RT_TUNE_GREEDY_WIDE) != 0;
+    if (ctx->hasWide && ctx->wideGreedy == greedy) return B2RT_OK;
     if (!ctx->hasBvh) return setError(ctx, B2RT_ERR_NO_BVH, "CudaTracer: No BVH!");
     std::vector<float> nodes(ctx->nodeBytes / 4), woop(ctx->woopBytes / 4);
     std::vector<int32_t> tri(ctx->triIndexBytes / 4);
@@ -111,17 +113,32 @@ int ensureWide(b2rt_ctx* ctx)
     if (ctx->triIndexBytes) B2RT_CUDA(ctx, cudaMemcpy(tri.data(), ctx->triIndex, ctx->triIndexBytes, cudaMemcpyDeviceToHost));
     Wide8 w;
     const char* err = "";
-    if (!buildWide8(nodes.data(), nodes.size() / 16, woop.data(), tri.data(), woop.size() / 4, w, &err))
+    if (!buildWide8(nodes.data(), nodes.size() / 16, woop.data(), tri.data(), woop.size() / 4, w, &err, greedy))
         return setError(ctx, B2RT_ERR_ARG, "wide BVH build failed: %s", err);
+    return uploadWide(ctx, w.nodes.data(), w.nodes.size() * 4, w.woop.data(), w.woop.size() * 4, w.triIndex.data(),
+                      w.triIndex.size() * 4, w.numNodes, w.numTris, w.maxDepth, greedy, false);
+}
+
+// The three arrays of the wide form go into ONE allocation (256-byte aligned parts), so that a single persisting-L2
+// access window can cover them (launchTraceWide).  srcIsDevice: the arrays are device memory already (b2rt_mg_broadcast_bvh).
+int uploadWide(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void* woop, size_t woopBytes, const void* tri,
+               size_t triBytes, int numNodes, int numTris, int maxDepth, bool greedy, bool srcIsDevice)
+{
     freeWide(ctx);
-    B2RT_CUDA(ctx, cudaMalloc(&ctx->wideNodes, w.nodes.size() * 4));
-    B2RT_CUDA(ctx, cudaMalloc(&ctx->wideWoop, w.woop.size() * 4));
-    B2RT_CUDA(ctx, cudaMalloc(&ctx->wideTriIndex, w.triIndex.size() * 4 + 16));
-    B2RT_CUDA(ctx, cudaMemcpy(ctx->wideNodes, w.nodes.data(), w.nodes.size() * 4, cudaMemcpyHostToDevice));
-    B2RT_CUDA(ctx, cudaMemcpy(ctx->wideWoop, w.woop.data(), w.woop.size() * 4, cudaMemcpyHostToDevice));
-    if (!w.triIndex.empty())
-        B2RT_CUDA(ctx, cudaMemcpy(ctx->wideTriIndex, w.triIndex.data(), w.triIndex.size() * 4, cudaMemcpyHostToDevice));
-    ctx->wideNumNodes = w.numNodes; ctx->wideNumTris = w.numTris;
+    auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
+    const size_t total = up(nodeBytes) + up(woopBytes) + up(triBytes + 16);
+    char* base = nullptr;
+    B2RT_CUDA(ctx, cudaMalloc(&base, total));
+    ctx->wideNodes = reinterpret_cast<float4*>(base);
+    ctx->wideWoop = reinterpret_cast<float4*>(base + up(nodeBytes));
+    ctx->wideTriIndex = reinterpret_cast<int32_t*>(base + up(nodeBytes) + up(woopBytes));
+    ctx->wideBytes = total;
+    const cudaMemcpyKind kind = srcIsDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    B2RT_CUDA(ctx, cudaMemcpy(ctx->wideNodes, nodes, nodeBytes, kind));
+    B2RT_CUDA(ctx, cudaMemcpy(ctx->wideWoop, woop, woopBytes, kind));
+    if (triBytes) B2RT_CUDA(ctx, cudaMemcpy(ctx->wideTriIndex, tri, triBytes, kind));
+    ctx->wideNumNodes = numNodes; ctx->wideNumTris = numTris; ctx->wideMaxDepth = maxDepth;
+    ctx->wideGreedy = greedy;
     ctx->hasWide = true;
     return B2RT_OK;
 }
@@ -176,7 +193,7 @@ void b2rt_destroy(b2rt_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaFree(ctx->nodes); cudaFree(ctx->woop); cudaFree(ctx->triIndex);
-    cudaFree(ctx->wideNodes); cudaFree(ctx->wideWoop); cudaFree(ctx->wideTriIndex);
+    cudaFree(ctx->wideNodes);
     cudaFree(ctx->shareList); cudaFree(ctx->warpCounter); cudaFree(ctx->statsDev); cudaFree(ctx->scratch);
     for (auto& slot : ctx->hostSlot) cudaFree(slot.stage);
     cudaFree(ctx->aabbDev); cudaFree(ctx->countDev); cudaFreeHost(ctx->countHost);

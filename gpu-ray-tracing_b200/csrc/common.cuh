@@ -5,7 +5,9 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <map>
 #include <string>
+#include <utility>
 
 #include "../../include/b2rt.h"
 
@@ -23,6 +25,7 @@ static_assert(sizeof(Ray) == 32 && sizeof(RayResult) == 16 && sizeof(MortonKey) 
 
 constexpr int kSentinel = B2RT_ENTRYPOINT_SENTINEL;
 constexpr int kTimelineWarps = 8192;    // per-warp exit times kept by the instrumented kernel (statsDev[16 ...])
+constexpr int kWideMaxDepth = 40;       // deepest 8-wide tree the wide kernel's 56-entry stack takes with room to postpone triangle groups
 constexpr size_t kWoopPadBytes = 64;   // private Woop copy: one terminator row + three zero rows past the caller's rows
 
 }  // namespace b2rt
@@ -45,10 +48,12 @@ struct b2rt_ctx {
 
     // second private form: 8-wide compressed nodes + re-packed Woop rows (wide_bvh.h), built on first use
     float4* wideNodes = nullptr; float4* wideWoop = nullptr; int32_t* wideTriIndex = nullptr;
-    int wideNumNodes = 0, wideNumTris = 0;
+    int wideNumNodes = 0, wideNumTris = 0, wideMaxDepth = 0;
+    size_t wideBytes = 0;       // the three arrays share one allocation (wideNodes is its start): one L2 access window covers them
     bool hasWide = false;
+    bool wideGreedy = false;    // the form in place was built with B2RT_TUNE_GREEDY_WIDE
 
-    b2rt_trace_config cfg = { -1, -1, -1, -1, -1 };
+    b2rt_trace_config cfg = { -1, -1, -1, -1, -1, 0u };
 
     // Launch slots: every trace launch takes the next of kLaunchSlots work counters (and, for the any-hit kernels, the
     // next slice of the shared-ray lists), so traces issued on different streams may overlap -- up to kLaunchSlots in flight.
@@ -68,6 +73,10 @@ struct b2rt_ctx {
         bool inFlight = false;
     } hostSlot[kHostSlots];
     int nextHostSlot = 0;
+
+    // per (kernel, dynamic shared memory): resident CTAs per SM, asked once (the attribute is set at the same time)
+    std::map<std::pair<const void*, size_t>, int> occupancy;
+    size_t l2SetAside = 0;     // bytes of L2 set aside for persisting accesses by this context (0 = never asked)
 
     int sortMode = 0;          // b2rt_set_sort_mode: 0 = prefix sort + tie settling (falls back by itself), 1 = always the full LSD sort
     int sortFellBack = 0;      // the last b2rt_morton_sort went the long way
@@ -103,6 +112,22 @@ extern std::string g_createError;
         (ctx)->launches++;                                                                     \
     } while (0)
 
+// cudaFuncSetAttribute + the occupancy query, once per (kernel, shared-memory size) instead of on every launch
+template <class K>
+int kernelOccupancy(b2rt_ctx* ctx, K kern, int block, size_t smem, int* blocksPerSm)
+{
+    const std::pair<const void*, size_t> key(reinterpret_cast<const void*>(kern), smem);
+    auto it = ctx->occupancy.find(key);
+    if (it == ctx->occupancy.end()) {
+        int n = 0;
+        B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, block, smem));
+        it = ctx->occupancy.emplace(key, n).first;
+    }
+    *blocksPerSm = it->second;
+    return B2RT_OK;
+}
+
 // kernels' launchers (defined in the .cu files)
 int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags,
                 cudaStream_t stream);
@@ -110,6 +135,8 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
                     cudaStream_t stream);
 int ensureWide(b2rt_ctx* ctx);      // builds the wide form from the private Compact2 copy if it is not there yet
+int uploadWide(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void* woop, size_t woopBytes, const void* tri,
+               size_t triBytes, int numNodes, int numTris, int maxDepth, bool greedy, bool srcIsDevice);
 
 int countWork(b2rt_ctx* ctx, const void* rays, int64_t numRays, int anyHit, b2rt_work_counters* out, cudaStream_t stream);
 
@@ -134,10 +161,6 @@ __device__ __forceinline__ int2 lds64i(unsigned addr)
     int2 v;
     asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
     return v;
-}
-__device__ __forceinline__ void prefetchL2(const void* p)
-{
-    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
 }
 __device__ __forceinline__ unsigned long long globalTimerNs()
 {

@@ -33,7 +33,7 @@ struct TraceParams {
     int fetchThreshold;
     int dummyLeaf;          // ~row of the terminator row behind the caller's Woop rows: a leaf without triangles (SHARE)
     int* shareList;         // SHARE: kShareList ray indices per CTA
-    int pfNodeLines, pfWoopLines;   // 128-byte lines of the node / Woop arrays to pull into L2 when the launch starts (0 = none)
+    int streamRays;         // 1: rays are read and records written with the streaming (evict-first) policy: they pass once, the BVH stays in L2
     int* warpCounter;
     unsigned long long* stats;
 };
@@ -80,14 +80,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
     int* s_stack = reinterpret_cast<int*>(s_dyn) + threadIdx.x;              // slot k at s_stack[k * BLOCK]
     const int topF4 = p.topF4;
     const int topNodes = topF4 >> 2;
-    // A launch that finds the BVH in DRAM pays a full miss on every step of every ray's dependent chain until the
-    // arrays have drifted into L2 by themselves.  Ask for them up front instead: one prefetch per 128-byte line,
-    // spread over the grid, streams at DRAM bandwidth (tens of MB: a few microseconds) behind the first rays.
-    {
-        const size_t stride = (size_t)gridDim.x * BLOCK;
-        for (size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x; i < (size_t)p.pfNodeLines; i += stride) prefetchL2(p.nodes + i * 8);
-        for (size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x; i < (size_t)p.pfWoopLines; i += stride) prefetchL2(p.woop + i * 8);
-    }
     float4* s_plane = s_dyn + (STACK_SMEM * BLOCK) / 4;
     {
         int2* s_child = reinterpret_cast<int2*>(s_plane + 3 * topNodes);
@@ -156,8 +148,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                               ((unsigned long long)__float_as_uint(hitT) << 32) | (unsigned)hitIndex);
             } else {
                 const int id = (hitIndex == -1) ? -1 : __ldg(p.triIndex + hitIndex);
-                if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
-                else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
+                if (BARY) {
+                    const int4 r = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
+                    if (p.streamRays) __stcs(p.results + rayidx, r); else p.results[rayidx] = r;
+                } else {
+                    int2* dst = reinterpret_cast<int2*>(p.results + rayidx);      // 8 of the record's 16 bytes (CudaTracerKernels.hh:197)
+                    const int2 r = make_int2(id, __float_as_int(hitT));
+                    if (p.streamRays) __stcs(dst, r); else *dst = r;
+                }
             }
             rayidx = -1;
         }
@@ -171,21 +169,23 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
             if (__shfl_sync(kFull, idle, 0) > 0) poolEmpty = true;
         }
         if (maskT != 0 && !poolEmpty) {
-            const int numT = __popc(maskT);
+            // unsigned arithmetic: the counter runs past numRays by up to one fetch per warp, which must not wrap for batches near 2^31 rays
+            const unsigned numT = __popc(maskT);
             const int leader = __ffs(maskT) - 1;
-            int base = 0;
-            if (lane == leader) base = atomicAdd(p.warpCounter, numT);
+            unsigned base = 0;
+            if (lane == leader) base = (unsigned)atomicAdd(p.warpCounter, (int)numT);
             base = __shfl_sync(kFull, base, leader);
             if (STATS && lane == leader) stFetches++;
-            if (STATS && base < p.numRays) { stLastFetch = globalTimerNs(); stItersAtFetch = warpSum(stNodeIters) + (warpSum(stTriIters) << 32); }
-            poolEmpty = (base + numT >= p.numRays);
+            if (STATS && base < (unsigned)p.numRays) { stLastFetch = globalTimerNs(); stItersAtFetch = warpSum(stNodeIters) + (warpSum(stTriIters) << 32); }
+            poolEmpty = (base + numT >= (unsigned)p.numRays);
             if (STATS && poolEmpty) stPoolEmpty = globalTimerNs();
             if (terminated) {
-                const int idx = base + __popc(maskT & ((1u << lane) - 1u));
-                if (idx < p.numRays) {
-                    rayidx = idx;
-                    const float4 o = ldg4(p.rays + 2 * (size_t)idx);
-                    const float4 d = ldg4(p.rays + 2 * (size_t)idx + 1);
+                const unsigned idx = base + __popc(maskT & ((1u << lane) - 1u));
+                if (idx < (unsigned)p.numRays) {
+                    rayidx = (int)idx;
+                    float4 o, d;
+                    if (p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
+                    else { o = ldg4(p.rays + 2 * (size_t)idx); d = ldg4(p.rays + 2 * (size_t)idx + 1); }
                     origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
                     dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
                     const float ooeps = 8.271806125530277e-25f;    // 2^-80, avoids division by zero
@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                 }
             }
             if (BARY) p.results[r] = make_int4(id, __float_as_int(t), __float_as_int(u), __float_as_int(v));
-            else reinterpret_cast<int2*>(p.results)[r * 2] = make_int2(id, __float_as_int(t));
+            else *reinterpret_cast<int2*>(p.results + r) = make_int2(id, __float_as_int(t));
         }
     }
 
@@ -524,9 +524,8 @@ static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
     while (topNodes > 0 && (size_t)topNodes * 56 + stackBytes > smemBudget) topNodes = (topNodes / 2) & ~7;
     p.topF4 = topNodes * 4;
     size_t smem = (size_t)topNodes * 56 + stackBytes;
-    B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int blocksPerSm = 0;
-    B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, smem));
+    { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
     long long grid = (long long)ctx->smCount * blocksPerSm;
@@ -577,13 +576,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     p.numRays = (int)numRays;
     p.topF4 = 0;
     p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 20 : ctx->cfg.fetch_threshold;
-    {
-        // off unless asked for: measured on C2 (32 MB of BVH) it buys +0.3 % behind an L2 flush and costs 1-2 % when
-        // the arrays are already resident (profiles/README.md)
-        const bool on = ctx->cfg.l2_prefetch > 0;
-        p.pfNodeLines = on ? (int)std::min<size_t>(ctx->nodeBytes / 128, 1u << 20) : 0;
-        p.pfWoopLines = on ? (int)std::min<size_t>(ctx->woopBytes / 128, 1u << 20) : 0;
-    }
+    p.streamRays = (ctx->cfg.tune & B2RT_TUNE_NO_STREAM) ? 0 : 1;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.dummyLeaf = ~(int)(ctx->woopBytes / 16);       // first padding row: a terminator (api.cu:b2rt_set_bvh)
@@ -605,7 +598,12 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
         // ray: knot 910 K triangles (70 MB of nodes + Woop rows): AO any-hit 3 100 vs 2 900, 64 Mi diffuse rays 3 210 vs
         // 3 020; strands 6.5 M triangles (1.2 GB): 574 vs 425.  On the 351 K-triangle interior (32 MB) the binary kernel
         // keeps a 25 % lead (4 800 vs 3 780), so the switch is the size of the two arrays.
-        if (ctx->nodeBytes + ctx->woopBytes > (size_t(48) << 20)) variant = 108;
+        if (ctx->nodeBytes + ctx->woopBytes > (size_t(48) << 20)) {
+            // ... unless the collapsed tree is too deep for that kernel's stack (a degenerate caller-built BVH): stay binary
+            const int rc = ensureWide(ctx);
+            if (rc) return rc;
+            if (ctx->wideMaxDepth <= kWideMaxDepth) variant = 108;
+        }
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {

@@ -27,12 +27,18 @@ struct WideParams {
     const int* __restrict__ triIndex;       // 1 per triangle
     int numRays;
     int fetchThreshold;
+    int pushLimit;                          // a triangle group may be postponed only while fewer than this many entries are stacked
+    int streamRays;                         // 1: rays are read and records written with the streaming (evict-first) policy
+    int refill;                             // 1: a fetch that brought degenerate rays is repeated until enough lanes are alive
     int* warpCounter;
     unsigned long long* stats;
     unsigned one;                           // 0x3F800000, passed as data so PRMT keeps its selector as the immediate
 };
 
-constexpr int kWideStack = 48;          // group entries; the collapsed tree is at most as deep as the binary one (<= 64, typ. < 12)
+// Stack capacity is kWideStack + SSLOTS entries.  Every level of the wide tree can leave one sibling group on the stack and
+// those pushes cannot be refused, so triangle groups are postponed only below WideParams::pushLimit = capacity - depth - 1 and
+// the launcher sends trees deeper than capacity - 2 to the binary kernel (trace.cu:launchTrace).
+constexpr int kWideStack = 48;
 constexpr unsigned kFullMask = 0xffffffffu;
 
 // byte j of `word` as the float 1 + byte * 2^-15 (exact): one PRMT, no integer-to-float conversion
@@ -46,9 +52,23 @@ __device__ __forceinline__ float byteToUnitFloat(unsigned word, unsigned one)
     return __uint_as_float(r);
 }
 
+template <bool BARY>
+__device__ __forceinline__ void storeResultT(const WideParams& p, unsigned rayidx, int id, float t, float u, float v)
+{
+    if (BARY) {
+        const int4 r = make_int4(id, __float_as_int(t), __float_as_int(u), __float_as_int(v));
+        if (p.streamRays) __stcs(p.results + rayidx, r); else p.results[rayidx] = r;
+    } else {
+        int2* dst = reinterpret_cast<int2*>(p.results + rayidx);           // 8 of the record's 16 bytes (CudaTracerKernels.hh:197)
+        const int2 r = make_int2(id, __float_as_int(t));
+        if (p.streamRays) __stcs(dst, r); else *dst = r;
+    }
+}
+
 template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
+    auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
     const int lane = threadIdx.x & 31;
     // Traversal stack: the first SSLOTS entries in shared memory (slot k of this thread at s_stack[k * BLOCK]: consecutive
     // threads, consecutive 8-byte words), the rest in local memory.  Entirely in local memory (SSLOTS == 0) the stack moved
@@ -80,45 +100,56 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         // ---- store finished rays, refill (same scheme as trace.cu) ----------------------------
         if (!active && rayidx >= 0) {
             const int id = (hitIndex < 0) ? -1 : __ldg(p.triIndex + hitIndex);
-            if (BARY) p.results[rayidx] = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
-            else reinterpret_cast<int2*>(p.results)[rayidx * 2] = make_int2(id, __float_as_int(hitT));
+            storeResult(p, (unsigned)rayidx, id, hitT, hitU, hitV);
             rayidx = -1;
         }
-        const unsigned maskT = __ballot_sync(kFullMask, !active);
-        if (maskT != 0 && !poolEmpty) {
-            const int numT = __popc(maskT);
+        for (;;) {
+            const unsigned maskT = __ballot_sync(kFullMask, !active);
+            if (maskT == 0 || poolEmpty) break;
+            const unsigned numT = __popc(maskT);
             const int leader = __ffs(maskT) - 1;
-            int base = 0;
-            if (lane == leader) base = atomicAdd(p.warpCounter, numT);
+            unsigned base = 0;
+            if (lane == leader) base = (unsigned)atomicAdd(p.warpCounter, (int)numT);
             base = __shfl_sync(kFullMask, base, leader);
             if (STATS && lane == leader) stFetches++;
-            poolEmpty = (base + numT >= p.numRays);
+            poolEmpty = (base + numT >= (unsigned)p.numRays);
+            bool degenerate = false;
             if (!active) {
-                const int idx = base + __popc(maskT & ((1u << lane) - 1u));
-                if (idx < p.numRays) {
-                    rayidx = idx;
-                    const float4 o = ldg4(p.rays + 2 * (size_t)idx);
-                    const float4 d = ldg4(p.rays + 2 * (size_t)idx + 1);
-                    origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
-                    dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
-                    const float ooeps = 8.271806125530277e-25f;    // 2^-80 (kepler_dynamic_fetch.cu:134-137)
-                    idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-                    idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-                    idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-                    // bit set <=> the ray travels towards + on that axis; replicated into four bytes
-                    octinv4 = ((idirx < 0.0f ? 0u : 4u) | (idiry < 0.0f ? 0u : 2u) | (idirz < 0.0f ? 0u : 1u)) * 0x01010101u;
-                    G = make_uint2(0u, 0x80000000u);               // the root, as a group of one
-                    T = make_uint2(0u, 0u);
-                    sp = 0; hitIndex = -1;
-                    // a degenerate ray (tmax < tmin, RayGenKernels.cu:223) can hit nothing: finish it here
-                    active = !(hitT < tmin);
+                const unsigned idx = base + __popc(maskT & ((1u << lane) - 1u));
+                if (idx < (unsigned)p.numRays) {
+                    float4 o, d;
+                    if (p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
+                    else { o = ldg4(p.rays + 2 * (size_t)idx); d = ldg4(p.rays + 2 * (size_t)idx + 1); }
+                    if (d.w < o.w) {
+                        // a degenerate ray (tmax < tmin, RayGenKernels.cu:223) can hit nothing: its record is written here
+                        storeResult(p, idx, -1, d.w, 0.0f, 0.0f);
+                        degenerate = true;
+                    } else {
+                        rayidx = (int)idx;
+                        origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
+                        dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
+                        const float ooeps = 8.271806125530277e-25f;    // 2^-80 (kepler_dynamic_fetch.cu:134-137)
+                        idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+                        idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+                        idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+                        // bit set <=> the ray travels towards + on that axis; replicated into four bytes
+                        octinv4 = ((idirx < 0.0f ? 0u : 4u) | (idiry < 0.0f ? 0u : 2u) | (idirz < 0.0f ? 0u : 1u)) * 0x01010101u;
+                        G = make_uint2(0u, 0x80000000u);               // the root, as a group of one
+                        T = make_uint2(0u, 0u);
+                        sp = 0; hitIndex = -1;
+                        if (BARY) { hitU = 0.0f; hitV = 0.0f; }
+                        active = true;
+                    }
                 }
             }
+            // Secondary batches carry runs of degenerate rays (one per sample of a primary ray that missed: 52 % of the C5
+            // batch).  A fetch that brought some would leave the warp short of live lanes for a whole node step, so it is
+            // repeated until the refill threshold is met or the pool is dry.
+            if (__ballot_sync(kFullMask, degenerate) == 0) break;
+            if (p.refill && __popc(__ballot_sync(kFullMask, active)) >= p.fetchThreshold) break;
+            if (!p.refill && __ballot_sync(kFullMask, active) != 0) break;
         }
-        if (__ballot_sync(kFullMask, active) == 0) {
-            if (__ballot_sync(kFullMask, rayidx >= 0) == 0) break;  // nothing in flight, nothing to store: the pool is empty
-            continue;                                               // only degenerate rays were fetched: store them, fetch again
-        }
+        if (__ballot_sync(kFullMask, active) == 0) break;              // nothing in flight and the pool is dry
         const int threshold = poolEmpty ? 0 : p.fetchThreshold;
 
         while (active) {
@@ -191,7 +222,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 int tri = (int)T.x + (T.y ? __ffs(T.y) - 1 : 0);
                 float4 v00 = ldg4(p.woop + (size_t)tri * 3);
                 while (T.y != 0u) {
-                    if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < kWideStack - 2) {
+                    if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < p.pushLimit) {
                         push(sp, T);
                         break;
                     }
@@ -219,7 +250,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 }
             } else
             while (T.y != 0u) {
-                if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < kWideStack - 2) {
+                if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < p.pushLimit) {
                     push(sp, T);
                     break;
                 }
@@ -284,8 +315,7 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>;
     int blocksPerSm = 0;
     const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2);
-    B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kern, BLOCK, smem));
+    { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
     long long grid = (long long)ctx->smCount * blocksPerSm;
@@ -293,8 +323,25 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     if (grid > needed) grid = needed;
     if (grid < 1) grid = 1;
     p.warpCounter = ctx->warpCounter + (ctx->launchSlot++ % b2rt_ctx::kLaunchSlots) * 32;
+    // stack: SSLOTS entries in shared memory + kWideStack in local memory; sibling groups (at most one per level) must always fit
+    p.pushLimit = kWideStack + SSLOTS - ctx->wideMaxDepth - 1;
+    if (p.pushLimit < 1) return setError(ctx, B2RT_ERR_ARG, "wide BVH is %d levels deep: too deep for the wide kernel's stack", ctx->wideMaxDepth);
     B2RT_CUDA(ctx, cudaMemsetAsync(p.warpCounter, 0, sizeof(int), stream));
-    kern<<<(unsigned)grid, BLOCK, smem, stream>>>(p);
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)grid); lc.blockDim = dim3(BLOCK); lc.dynamicSmemBytes = smem; lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    lc.attrs = attr; lc.numAttrs = 0;
+    if ((ctx->cfg.tune & B2RT_TUNE_L2_WINDOW) && ctx->l2SetAside >= ctx->wideBytes) {
+        // the whole wide form (nodes, Woop rows, ids: one allocation) stays in the set-aside part of L2; rays and records stream past it
+        attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[0].val.accessPolicyWindow.base_ptr = ctx->wideNodes;
+        attr[0].val.accessPolicyWindow.num_bytes = ctx->wideBytes;
+        attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
+        attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        lc.numAttrs = 1;
+    }
+    B2RT_CUDA(ctx, cudaLaunchKernelEx(&lc, kern, p));
     B2RT_CHECK_LAUNCH(ctx, "traceWideKernel");
     return B2RT_OK;
 }
@@ -318,6 +365,13 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
 {
     int rc = ensureWide(ctx);
     if (rc) return rc;
+    if ((ctx->cfg.tune & B2RT_TUNE_L2_WINDOW) && ctx->l2SetAside == 0) {
+        // ask once for as much persisting L2 as the device gives (device-wide limit; other kernels simply do not use it)
+        cudaDeviceProp prop;
+        B2RT_CUDA(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+        B2RT_CUDA(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize));
+        ctx->l2SetAside = (size_t)prop.persistingL2CacheMaxSize;
+    }
     WideParams p;
     p.rays = static_cast<const float4*>(rays);
     p.results = static_cast<int4*>(results);
@@ -332,6 +386,9 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
+    p.streamRays = (ctx->cfg.tune & B2RT_TUNE_NO_STREAM) ? 0 : 1;
+    p.refill = (ctx->cfg.tune & B2RT_TUNE_NO_REFILL) ? 0 : 1;
+    p.pushLimit = 0;
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
     switch (variant) {
     default:

@@ -18,7 +18,10 @@
 //   q2: qlo_x[0..7], qlo_y[0..7]      q3: qlo_z[0..7], qhi_x[0..7]      q4: qhi_y[0..7], qhi_z[0..7]
 // meta[i]: 0 = empty slot; inner child: 0b001_11sss (sss = slot i), also bit i of imask; leaf child:
 // high 3 bits = triangle count in unary (1, 3, 7), low 5 bits = first triangle relative to triBase.
-// Child box i = p + 2^(e-15-127) * 2^15 * q  (see trace_wide.cu for the decode).
+// Child box i = p + 2^e * q, e = byte - 142 (see trace_wide.cu for the decode).  The boxes are conservative supersets of the
+// binary tree's WITH the kernel's rounding: each plane is quantised with 1/64 of a cell of slack (host/wide_bvh.cpp).
+// Which binary nodes are folded into one wide node is decided by a dynamic programme over the binary tree that minimises
+// the SAH cost of the result (Ylitie et al., section 3.1); subtrees with at most three triangle references become one leaf slot.
 #pragma once
 
 #include <stddef.h>
@@ -40,10 +43,12 @@ struct Wide8 {
 // Collapse.  nodes2: Compact2 nodes (16 floats each, caller's order, root = node 0); woop / triIndex: the
 // caller's rows.  Returns false (with a message) on malformed input.
 bool buildWide8(const float* nodes2, size_t numNodes2, const float* woop, const int32_t* triIndex, size_t numRows,
-                Wide8& out, const char** error);
+                Wide8& out, const char** error, bool greedy = false);
 
-// Structural check used by the CPU tests: every triangle reference of the binary tree appears exactly
-// once, every decoded child box contains the binary tree's box, indices are in range.
+// Structural check used by the CPU tests: every triangle reference of the binary tree appears exactly once, every
+// wide node is reachable exactly once, indices are in range.  (That every quantised child box contains the binary
+// tree's box with at least half a margin to spare is checked by buildWide8 itself while it emits a node -- it is the
+// only place that still knows which binary box a slot came from -- and makes the build fail.)
 bool validateWide8(const float* nodes2, size_t numNodes2, const float* woop, const int32_t* triIndex, size_t numRows,
                    const Wide8& w, const char** error);
 

@@ -62,8 +62,8 @@ class Context:
         check(lib().b2rt_device_info(self.handle, C.byref(sm), None, None), self.handle)
         return sm.value
 
-    def set_trace_config(self, top_nodes=-1, fetch_threshold=-1, blocks_per_sm=-1, variant=-1, l2_prefetch=-1):
-        cfg = TraceConfig(top_nodes, fetch_threshold, blocks_per_sm, variant, l2_prefetch)
+    def set_trace_config(self, top_nodes=-1, fetch_threshold=-1, blocks_per_sm=-1, variant=-1, l2_prefetch=-1, tune=0):
+        cfg = TraceConfig(top_nodes, fetch_threshold, blocks_per_sm, variant, l2_prefetch, tune)
         check(lib().b2rt_set_trace_config(self.handle, C.byref(cfg)), self.handle)
 
     def set_sort_mode(self, mode=0):

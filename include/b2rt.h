@@ -86,9 +86,15 @@ typedef struct {
                                    (kepler_dynamic_fetch.cu:48 uses 20); -1 = default: 20, 24 in the 8-wide kernel */
     int blocks_per_sm;          /* persistent CTAs per SM; -1 = from occupancy */
     int variant;                /* kernel variant id; -1 = chosen from the batch size and the size of the BVH (trace.cu:launchTrace) */
-    int l2_prefetch;            /* 1: every launch starts by pulling the private BVH arrays into L2 (bulk reads instead of
-                                   cold misses on the rays' dependent chains); 0 or -1: off (no measured gain) */
+    int l2_prefetch;            /* reserved (was: pull the BVH into L2 at launch start; measured no gain, removed); ignored */
+    unsigned tune;              /* B2RT_TUNE_* bits that switch single design decisions OFF for A/B measurements; 0 = as shipped */
 } b2rt_trace_config;
+#define B2RT_TUNE_NO_STREAM      1u  /* rays / records through the normal cache policy instead of evict-first (ld.cs / st.cs) */
+#define B2RT_TUNE_NO_REFILL      2u  /* 8-wide kernel: do not repeat a fetch that brought degenerate rays */
+#define B2RT_TUNE_GREEDY_WIDE    4u  /* 8-wide form: round-1 greedy top-down collapse instead of the SAH-optimal one; takes effect
+                                        at the next b2rt_set_bvh */
+#define B2RT_TUNE_L2_WINDOW      8u  /* (opt-in) 8-wide kernel: persisting-L2 access window over the private wide arrays when they fit
+                                        the device's set-aside; sets the device-wide cudaLimitPersistingL2CacheSize */
 
 /* ---- context ---------------------------------------------------------------------------- */
 /* replaces CudaModule::staticInit + CudaTracer::CudaTracer (CudaTracer.cc:67-72) */

@@ -25,11 +25,17 @@ def median_ms(fn, warm=3, reps=7):
 
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "c2"
-    configs = [a for a in sys.argv[2:]]
+    configs = [a for a in sys.argv[2:] if not a.startswith("--")]
+    sort_batches = "--sorted" in sys.argv      # Morton-sort every secondary batch first (RayBuffer::mortonSort), untimed
     ctx = b2rt.Context.get(0)
     scene, bvh = wl.build_scene_and_bvh(name, log=lambda s: print(s, flush=True))
     frame = wl.Frame(name, scene, bvh.arrays(), "cuda:0", ctx)
     counted = frame.counted_rays()
+    if sort_batches:
+        for rb, _ in frame.batches:
+            if rb is not frame.primary:
+                rb.mortonSort(ctx)
+        print("batches Morton-sorted", flush=True)
     print("batches", [(b.getSize(), c) for b, c in frame.batches], flush=True)
     for rb, _ in frame.batches[:2]:
         work = frame.tracer.countWork(rb)
@@ -58,13 +64,16 @@ def main():
             if tok.startswith("t"): kw["top_nodes"] = int(tok[1:])
             if tok.startswith("f"): kw["fetch_threshold"] = int(tok[1:])
             if tok.startswith("b"): kw["blocks_per_sm"] = int(tok[1:])
-            if tok.startswith("p"): kw["l2_prefetch"] = int(tok[1:])
+            if tok.startswith("x"): kw["tune"] = int(tok[1:])
             if tok.startswith("o"): overlap = int(tok[1:])
         ctx.set_trace_config(**kw)
+        if kw.get("tune", 0) & 4 or getattr(main, "_was_greedy", False):
+            frame.tracer.setBVH(frame.cuda_bvh)         # the collapse mode takes effect at the next setBVH
+            main._was_greedy = bool(kw.get("tune", 0) & 4)
         ms = median_ms((lambda: frame.trace_all_overlapped(overlap)) if overlap else frame.trace_all)
         out[s] = counted / ms / 1e3
         print("%-16s %8.3f ms  %9.1f Mrays/s" % (s, ms, out[s]), flush=True)
-        if kw.get("variant", 0) < 100:
+        if True:
             # SIMD efficiency and launch timeline, per batch (instrumented kernel, same configuration)
             frame.tracer.collectStats = True
             for rb, _ in frame.batches[:2]:
