@@ -90,6 +90,9 @@ _SIGNATURES = {
     "b2rt_wide_build": (i32, [vp, sz, vp, sz, vp, sz, C.POINTER(vp)]),
     "b2rt_wide_free": (None, [vp]),
     "b2rt_wide_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), vp]),
+}
+
+_SCENE_SIGNATURES = {
     "b2rt_scene_generate": (i32, [i32, i32, C.c_uint64, C.POINTER(vp)]),
     "b2rt_scene_free": (None, [vp]),
     "b2rt_scene_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(i32), C.POINTER(vp), C.POINTER(i32)]),
@@ -97,7 +100,27 @@ _SIGNATURES = {
     "b2rt_scene_write_obj": (i32, [vp, C.c_char_p]),
 }
 
-EXPORTS = sorted(_SIGNATURES)
+# what include/b2rt.h declares, what include/b2rt_tools.h adds (instrumentation), what libb2rt_scenes.so exports
+TOOLS_EXPORTS = sorted(["b2rt_get_trace_stats", "b2rt_count_work", "b2rt_wide_build", "b2rt_wide_free", "b2rt_wide_arrays"])
+EXPORTS = sorted(n for n in _SIGNATURES if n not in TOOLS_EXPORTS)
+SCENES_EXPORTS = sorted(_SCENE_SIGNATURES)
+SCENES_LIB_PATH = os.path.join(HERE, "libb2rt_scenes.so")
+_scenes = None
+
+
+def scenes_lib():
+    """libb2rt_scenes.so: the procedural benchmark scenes (include/b2rt_scenes.h).  Host only."""
+    global _scenes
+    if _scenes is None:
+        if not os.path.exists(SCENES_LIB_PATH):
+            raise ImportError("libb2rt_scenes.so is not built: run `python gpu-ray-tracing_b200/build.py`")
+        l = C.CDLL(SCENES_LIB_PATH)
+        for name, (res, args) in _SCENE_SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _scenes = l
+    return _scenes
 
 
 def lib():

@@ -13,6 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libb2rt.so")
+SCENES_LIB = os.path.join(HERE, "libb2rt_scenes.so")      # benchmark scene generators (include/b2rt_scenes.h): host only, not part of libb2rt
 REFABI_LIB = os.path.join(HERE, "libb2rt_refabi.so")      # the reference's launcher ABI on top of libb2rt (include/b2rt_refabi.h)
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
@@ -33,7 +34,7 @@ CUDA_SOURCES = [
     ("misc.cu", ["-fmad=false"]),
     ("woopify.cu", ["-fmad=false"]),
 ]
-HOST_SOURCES = ["host/bvh_builder.cpp", "host/scenegen.cpp", "host/host_util.cpp", "host/wide_bvh.cpp"]
+HOST_SOURCES = ["host/bvh_builder.cpp", "host/host_util.cpp", "host/wide_bvh.cpp"]
 HOST_FLAGS = ["-O2", "-ffp-contract=off", "-fPIC", "-std=c++17", "-pthread", "-Wall", "-I", INCLUDE]
 
 
@@ -56,7 +57,8 @@ def _run(cmd, verbose):
 
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
-    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "wide_bvh.h"), os.path.join(INCLUDE, "b2rt.h"), os.path.abspath(__file__)]
+    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "wide_bvh.h"), os.path.join(INCLUDE, "b2rt.h"),
+               os.path.join(INCLUDE, "b2rt_tools.h"), os.path.abspath(__file__)]
     objs = []
     log = []
     for src, extra in CUDA_SOURCES:
@@ -73,6 +75,9 @@ def build(force=False, verbose=False):
             log.append(_run([CXX] + HOST_FLAGS + ["-c", s, "-o", o], verbose))
     if force or not _newer(LIB, objs):
         log.append(_run([NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lpthread"], verbose))
+    scenes_src = os.path.join(CSRC, "host", "scenegen.cpp")
+    if force or not _newer(SCENES_LIB, [scenes_src, os.path.join(INCLUDE, "b2rt_scenes.h"), os.path.abspath(__file__)]):
+        log.append(_run([CXX] + HOST_FLAGS + ["-shared", scenes_src, "-o", SCENES_LIB], verbose))
     refabi_src = os.path.join(CSRC, "host", "refabi.cpp")
     if force or not _newer(REFABI_LIB, [refabi_src, LIB, os.path.join(INCLUDE, "b2rt_refabi.h")] + headers):
         cuda_home = os.path.dirname(os.path.dirname(NVCC))

@@ -10,6 +10,7 @@
 #include <utility>
 
 #include "../../include/b2rt.h"
+#include "../../include/b2rt_tools.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
 #error "libb2rt is written for sm_100a (B200) only"

@@ -18,7 +18,10 @@
 #include <algorithm>
 #include <vector>
 
-#include "../../../include/b2rt.h"
+#include "../../../include/b2rt_scenes.h"
+
+#define B2RT_OK 0
+#define B2RT_ERR_ARG (-1)
 
 struct b2rt_scene {
     std::vector<float> verts;

@@ -462,7 +462,7 @@ bool validateWide8(const float* nodes2, size_t numNodes2, const float* woop, con
 }  // namespace b2rt
 
 // ---- C ABI (host only): build / inspect the wide form without a GPU (tests, tooling) ----
-#include "../../../include/b2rt.h"
+#include "../../../include/b2rt_tools.h"
 
 struct b2rt_wide_bvh { b2rt::Wide8 w; };
 

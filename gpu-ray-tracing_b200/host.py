@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 from ._lib import (BuildParams, B2rtError, LAYOUT_COMPACT2, RAY_DTYPE, RESULT_DTYPE, TRACE_ANY_HIT,
-                   TRACE_STATS, TRACE_WRITE_BARY, TraceConfig, TraceStats, check, lib, np_ptr)
+                   TRACE_STATS, TRACE_WRITE_BARY, TraceConfig, TraceStats, check, lib, np_ptr, scenes_lib)
 
 SCENE_KINDS = {"blob": 0, "interior": 1, "knot": 2, "strands": 3}
 
@@ -92,19 +92,21 @@ class Scene:
 
     @staticmethod
     def generate(kind, target_tris, seed):
-        """Seeded procedural stand-in for a README scene (csrc/host/scenegen.cpp)."""
+        """Seeded procedural stand-in for a README scene (libb2rt_scenes.so, csrc/host/scenegen.cpp)."""
+        sl = scenes_lib()
         h = C.c_void_p()
-        check(lib().b2rt_scene_generate(SCENE_KINDS[kind], int(target_tris), C.c_uint64(seed), C.byref(h)))
+        if sl.b2rt_scene_generate(SCENE_KINDS[kind], int(target_tris), C.c_uint64(seed), C.byref(h)) != 0:
+            raise ValueError("b2rt_scene_generate(%s, %d) failed" % (kind, target_tris))
         try:
             v, t = C.c_void_p(), C.c_void_p()
             nv, nt = C.c_int(), C.c_int()
-            check(lib().b2rt_scene_arrays(h, C.byref(v), C.byref(nv), C.byref(t), C.byref(nt)))
+            sl.b2rt_scene_arrays(h, C.byref(v), C.byref(nv), C.byref(t), C.byref(nt))
             verts = np.ctypeslib.as_array(C.cast(v, C.POINTER(C.c_float)), (nv.value, 3)).copy()
             tris = np.ctypeslib.as_array(C.cast(t, C.POINTER(C.c_int32)), (nt.value, 3)).copy()
             cam = np.empty(12, np.float32)
-            check(lib().b2rt_scene_camera(h, np_ptr(cam)))
+            sl.b2rt_scene_camera(h, np_ptr(cam))
         finally:
-            lib().b2rt_scene_free(h)
+            sl.b2rt_scene_free(h)
         camera = {"pos": cam[0:3].copy(), "forward": cam[3:6].copy(), "up": cam[6:9].copy(),
                   "fov": float(cam[9]), "near": float(cam[10]), "far": float(cam[11])}
         return Scene(verts, tris, camera, name="%s-%d" % (kind, target_tris))

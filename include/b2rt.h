@@ -56,28 +56,7 @@ typedef enum {
 /* b2rt_trace flags */
 #define B2RT_TRACE_ANY_HIT     1u  /* !RayBuffer::getNeedClosestHit()              CudaTracer.cc:172 */
 #define B2RT_TRACE_WRITE_BARY  2u  /* store u,v in RayResult.padA/padB             (superset) */
-#define B2RT_TRACE_STATS       4u  /* instrumented kernel: fills b2rt_trace_stats  (slower) */
-
-/* SIMD-efficiency counters of the instrumented kernel (README.md:46-81 TRV / IST columns:
- * mean active lanes / 32 over node-loop and triangle-loop iterations). */
-typedef struct {
-    uint64_t node_iters;        /* warp-level node-loop iterations */
-    uint64_t node_lanes;        /* active lanes summed over them */
-    uint64_t tri_iters;         /* warp-level triangle-loop iterations */
-    uint64_t tri_lanes;
-    uint64_t fetches;           /* warp-level ray fetches (atomics on the work counter) */
-    uint64_t rays;
-    /* launch timeline from the global timer (binary kernel): nanoseconds after the first warp started */
-    uint64_t warps;             /* persistent warps that ran */
-    uint64_t ns_pool_empty;     /* first warp found the work counter past the last ray */
-    uint64_t ns_mean_exit;      /* mean warp exit time */
-    uint64_t ns_last_exit;      /* last warp exit = length of the launch; (last - mean) / last = idle tail */
-    uint64_t ns_exit_p50, ns_exit_p90, ns_exit_p99;    /* percentiles of the per-warp exit times */
-    /* the warp that left last: when it fetched its last rays, and the loop iterations it ran from then on --
-     * the launch cannot end before that one bundle's dependent chain of node and triangle steps has */
-    uint64_t ns_straggler_fetch, straggler_node_iters, straggler_tri_iters;
-    uint64_t shares;            /* any-hit kernels: stack entries handed to idle lanes after the pool ran dry */
-} b2rt_trace_stats;
+#define B2RT_TRACE_STATS       4u  /* instrumented kernel: fills b2rt_trace_stats (include/b2rt_tools.h; slower) */
 
 /* Tunables of the traversal kernel; zero-initialise and override what you need. */
 typedef struct {
@@ -139,20 +118,6 @@ int b2rt_trace_host(b2rt_ctx* ctx, const void* rays_host, void* results_host, in
  * the first upload to the last download.  The host buffers must stay valid, and the results unread, until _end. */
 int b2rt_trace_host_begin(b2rt_ctx* ctx, const void* rays_host, void* results_host, int64_t num_rays, unsigned flags);
 int b2rt_trace_host_end(b2rt_ctx* ctx, float* ms_kernel, float* ms_total);
-/* counters of the last B2RT_TRACE_STATS launch (synchronises) */
-int b2rt_get_trace_stats(b2rt_ctx* ctx, b2rt_trace_stats* out);
-
-/* Algorithmic work of a batch: per-ray counters of the CANONICAL traversal (near-first ordered
- * stack traversal of the Compact2 arrays, Woop test, closest-hit pruning or any-hit exit, no
- * speculation, no postponement, IEEE division) summed over the batch -- the N_n, N_t, N_l, N_u,
- * N_v, h of SURVEY.md 8(d) from which bench.py computes the roofline's algorithmic bytes.  A plain
- * one-thread-per-ray kernel, not the production tracer.  Synchronous. */
-typedef struct {
-    uint64_t rays, nodes, tris, leaves, ustage, vstage, hits, max_stack;
-    uint64_t max_chain;         /* largest (node visits + triangle tests) of a single ray: the serial tail of a launch */
-} b2rt_work_counters;
-int b2rt_count_work(b2rt_ctx* ctx, const void* rays_dev, int64_t num_rays, int any_hit,
-                    b2rt_work_counters* out, void* stream);
 
 /* ---- ray generation --------------------------------------------------------------------- */
 /* replaces launch_rayGenPrimaryKernel (ray/RayGenKernels.hh:40-51,107-109; RayGenKernels.cu:79-113).
@@ -246,29 +211,6 @@ int  b2rt_tri_normals(const float* verts, const int32_t* tris, int num_tris, flo
  * every row no reference covers becomes a leaf terminator (x = 0x80000000, CudaBVH.hh:47-50). */
 int  b2rt_woopify(b2rt_ctx* ctx, const float* verts, const int32_t* vtx_index, const int32_t* ref_row, const int32_t* ref_tri,
                   int64_t num_refs, void* woop, int64_t num_rows, void* stream);
-
-/* Private 8-wide compressed form of a Compact2 BVH (csrc/wide_bvh.h): what b2rt_set_bvh builds for the wide
- * traversal kernel (b2rt_trace_config.variant >= 100), exposed so it can be built and inspected without a GPU.
- * 80-byte nodes, re-packed Woop rows (3 per triangle, +2 padding rows), one original triangle id per triangle.
- * stats = { nodes, triangles, depth }. */
-typedef struct b2rt_wide_bvh b2rt_wide_bvh;
-int  b2rt_wide_build(const void* nodes, size_t node_bytes, const void* woop, size_t woop_bytes,
-                     const int32_t* tri_index, size_t tri_index_bytes, b2rt_wide_bvh** out);
-void b2rt_wide_free(b2rt_wide_bvh* w);
-int  b2rt_wide_arrays(const b2rt_wide_bvh* w, const void** nodes, size_t* node_bytes, const void** woop,
-                      size_t* woop_bytes, const int32_t** tri_index, size_t* tri_index_bytes, int stats[3]);
-
-/* Seeded procedural stand-ins for the README scenes (no network: bunny/conference/dragon/
- * hairball cannot be fetched).  kind: 0 blob (bunny-scale), 1 interior (conference-scale),
- * 2 knot (dragon-scale), 3 strands (hairball-scale).  SURVEY.md 8(d). */
-typedef struct b2rt_scene b2rt_scene;
-int  b2rt_scene_generate(int kind, int target_tris, uint64_t seed, b2rt_scene** out);
-void b2rt_scene_free(b2rt_scene* s);
-int  b2rt_scene_arrays(const b2rt_scene* s, const float** verts, int* num_verts,
-                       const int32_t** tris, int* num_tris);
-/* camera for the scene: position[3], forward[3], up[3], fov, near, far (12 floats) */
-int  b2rt_scene_camera(const b2rt_scene* s, float cam[12]);
-int  b2rt_scene_write_obj(const b2rt_scene* s, const char* path);
 
 #ifdef __cplusplus
 }

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include "b2rt_fw.hpp"
+#include "b2rt_scenes.h"
 #include "b2rt_oracle.h"
 
 namespace FW = b2rt_fw;

@@ -17,7 +17,7 @@ def _build(b2rt, oracle):
         return EXE
     cuda = "/usr/local/cuda"
     cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "oracle"),
-           "-I", cuda + "/include", src, "-o", EXE, "-L", PKG, "-lb2rt", "-L", os.path.join(ROOT, "oracle"), "-lb2rt_oracle",
+           "-I", cuda + "/include", src, "-o", EXE, "-L", PKG, "-lb2rt", "-lb2rt_scenes", "-L", os.path.join(ROOT, "oracle"), "-lb2rt_oracle",
            "-L", cuda + "/lib64", "-lcudart", "-Wl,-rpath," + PKG, "-Wl,-rpath," + os.path.join(ROOT, "oracle")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr

@@ -22,6 +22,14 @@ def test_header_symbols_exported(b2rt):
     missing = [n for n in names if not hasattr(lib, n)]
     assert not missing, "declared in include/b2rt.h but not exported: %s" % missing
     assert sorted(b2rt.EXPORTS) == names, "ctypes binding and header disagree"
+    # instrumentation entry points live in their own header (include/b2rt_tools.h), same library
+    tools = [n for n in _declared("b2rt_tools.h") if n not in names]
+    assert sorted(b2rt.TOOLS_EXPORTS) == tools and not [n for n in tools if not hasattr(lib, n)]
+    # the benchmark scenes are a separate host-only library (include/b2rt_scenes.h): nothing of it in libb2rt.so
+    scenes = _declared("b2rt_scenes.h")
+    sl = C.CDLL(b2rt.SCENES_LIB_PATH)
+    assert sorted(b2rt.SCENES_EXPORTS) == scenes and not [n for n in scenes if not hasattr(sl, n)]
+    assert not [n for n in scenes if hasattr(lib, n)]
 
 
 def test_reference_kernel_abi_exported(b2rt):
