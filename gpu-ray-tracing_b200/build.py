@@ -83,7 +83,7 @@ def build(force=False, verbose=False):
         cuda_home = os.path.dirname(os.path.dirname(NVCC))
         log.append(_run([CXX] + HOST_FLAGS + ["-I", os.path.join(cuda_home, "include"), "-shared", refabi_src, "-o", REFABI_LIB,
                          "-L", HERE, "-lb2rt", "-L", os.path.join(cuda_home, "lib64"), "-lcudart", "-Wl,-rpath,$ORIGIN"], verbose))
-    with open(os.path.join(OBJ, "build.log"), "a") as f:
+    with open(os.path.join(OBJ, "build.log"), "a" if not force else "w") as f:
         f.write("".join(log))
     return LIB
 

@@ -602,21 +602,25 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
             // ... unless the collapsed tree is too deep for that kernel's stack (a degenerate caller-built BVH): stay binary
             const int rc = ensureWide(ctx);
             if (rc) return rc;
-            if (ctx->wideMaxDepth <= kWideMaxDepth) variant = 108;
+            if (ctx->wideMaxDepth <= kWideMaxDepth)
+                variant = (numRays > (4 << 20) && !(ctx->cfg.tune & B2RT_TUNE_NO_RING)) ? 114 : 108;
         }
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
     switch (variant) {
     default:
+    case 1: return launchFlags<12, 256, 4>(ctx, p, flags, stream);      // four 256-thread CTAs per SM (<= 64 regs), reference-shaped leaf loop
+    case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // one 1024-thread CTA per SM, 2048-node shared top of the tree, look-ahead leaf loop
+    case 9: return launchFlags<12, 512, 2, 1>(ctx, p, flags, stream);   // two 512-thread CTAs per SM, look-ahead leaf loop (any-hit batches)
+    case 10: return launchFlags<12, 256, 4, 1>(ctx, p, flags, stream);  // variant 1 with the look-ahead leaf loop
+#ifdef B2RT_EXPLORE
+    // shapes measured in round 1 and not shipped; build with -DB2RT_EXPLORE to get them back
     case 0: return launchFlags<12, 256, 5>(ctx, p, flags, stream);   // <= 48 regs, 40 warps/SM
-    case 1: return launchFlags<12, 256, 4>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM
     case 2: return launchFlags<0, 256, 5>(ctx, p, flags, stream);    // stack entirely in local memory
     case 3: return launchFlags<16, 128, 8>(ctx, p, flags, stream);   // small CTAs
-    case 6: return launchFlags<12, 1024, 1>(ctx, p, flags, stream);  // one CTA per SM: one big shared top-of-tree
-    case 7: return launchFlags<12, 512, 2>(ctx, p, flags, stream);   // two CTAs per SM, <= 64 regs
-    case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // v6 with the look-ahead leaf loop
-    case 9: return launchFlags<12, 512, 2, 1>(ctx, p, flags, stream);   // v7 with the look-ahead leaf loop
-    case 10: return launchFlags<12, 256, 4, 1>(ctx, p, flags, stream);  // v1 with the look-ahead leaf loop
+    case 6: return launchFlags<12, 1024, 1>(ctx, p, flags, stream);  // variant 8 with the reference-shaped leaf loop
+    case 7: return launchFlags<12, 512, 2>(ctx, p, flags, stream);   // variant 9 with the reference-shaped leaf loop
+#endif
     }
 }
 

@@ -29,7 +29,6 @@ struct WideParams {
     int fetchThreshold;
     int pushLimit;                          // a triangle group may be postponed only while fewer than this many entries are stacked
     int streamRays;                         // 1: rays are read and records written with the streaming (evict-first) policy
-    int refill;                             // 1: a fetch that brought degenerate rays is repeated until enough lanes are alive
     int* warpCounter;
     unsigned long long* stats;
     unsigned one;                           // 0x3F800000, passed as data so PRMT keeps its selector as the immediate
@@ -65,7 +64,26 @@ __device__ __forceinline__ void storeResultT(const WideParams& p, unsigned rayid
     }
 }
 
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
+// FETCH == 1: rays reach a warp through a private two-chunk ring in shared memory instead of one atomic + one dependent global
+// load per refill.  ncu on the C5 batch: a warp refills 980 times per launch and every refill is a chain of an atomic on the
+// work counter (~1 us under load) and the ray load behind it (DRAM: the batch streams through once) during which the
+// warp's 20-odd live lanes wait -- a sixth of every warp's time.  Here chunks of kChunk rays are dealt out STATICALLY for the
+// first 7/8 of the batch (chunk r * warps + w goes to warp w in its round r: no atomic, the address of the chunk after next is
+// known, so it is copied into the ring with cp.async one refill ahead) and claimed from the work counter only for the last
+// eighth, which evens out what the static deal left unbalanced.  A refill then costs two shared-memory loads per lane.
+// Chosen for batches above 4 Mi rays only (launchTrace): a warp holds up to two chunks it has not started, which would
+// lengthen the tail of a frame-sized launch.
+constexpr int kChunk = 16;              // rays per chunk: the mean refill of the on-demand scheme is 14.5 rays
+constexpr int kRingBytes = 2 * kChunk * 32;     // per warp: two chunks of 32-byte rays
+
+__device__ __forceinline__ void cpAsync16(unsigned dstShared, const void* src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dstShared), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cpAsyncWaitAll() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, int FETCH>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
     auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
@@ -95,6 +113,61 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
     bool poolEmpty = false;
     unsigned long long stNodeIters = 0, stNodeLanes = 0, stTriIters = 0, stTriLanes = 0, stFetches = 0;
 
+    // a fetched ray becomes this lane's ray -- or, degenerate (tmax < tmin, RayGenKernels.cu:223: it can hit nothing), is answered on the spot
+    auto takeRay = [&](unsigned idx, const float4 o, const float4 d) {
+        if (d.w < o.w) { storeResult(p, idx, -1, d.w, 0.0f, 0.0f); return; }
+        rayidx = (int)idx;
+        origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
+        dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
+        const float ooeps = 8.271806125530277e-25f;    // 2^-80 (kepler_dynamic_fetch.cu:134-137)
+        idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+        idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+        idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+        // bit set <=> the ray travels towards + on that axis; replicated into four bytes
+        octinv4 = ((idirx < 0.0f ? 0u : 4u) | (idiry < 0.0f ? 0u : 2u) | (idirz < 0.0f ? 0u : 1u)) * 0x01010101u;
+        G = make_uint2(0u, 0x80000000u);               // the root, as a group of one
+        T = make_uint2(0u, 0u);
+        sp = 0; hitIndex = -1;
+        if (BARY) { hitU = 0.0f; hitV = 0.0f; }
+        active = true;
+    };
+
+    // FETCH == 1: the warp's ring and its place in the deal (all warp-uniform)
+    const unsigned ring = (unsigned)__cvta_generic_to_shared(s_wideStack) + (unsigned)(SSLOTS * BLOCK * sizeof(uint2)) +
+                          (unsigned)(threadIdx.x >> 5) * kRingBytes;
+    const unsigned numWarps = gridDim.x * (BLOCK / 32), warpId = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
+    const unsigned numChunks = ((unsigned)p.numRays + kChunk - 1) / kChunk;
+    const unsigned staticRounds = (numChunks / numWarps) - (numChunks / numWarps) / 8;
+    unsigned round = 0, headBase = 0, nextBase = 0;
+    int headCnt = 0, headPos = 0, nextCnt = 0, headHalf = 0;
+    auto claimChunk = [&]() -> unsigned {           // first ray of the warp's next chunk, 0xFFFFFFFF when the batch is dealt out
+        unsigned c;
+        if (round < staticRounds) c = round * numWarps + warpId;
+        else {
+            unsigned v = 0;
+            if (lane == 0) v = (unsigned)atomicAdd(p.warpCounter, 1);
+            c = staticRounds * numWarps + __shfl_sync(kFullMask, v, 0);
+            if (STATS && lane == 0) stFetches++;
+        }
+        round++;
+        return c < numChunks ? c * kChunk : 0xFFFFFFFFu;
+    };
+    auto loadChunk = [&](unsigned base, int half) {     // asynchronous copy of a chunk into one half of the ring
+        const unsigned long long i4 = (unsigned long long)base * 2 + lane;       // kChunk rays = 32 float4: one per lane
+        if (base != 0xFFFFFFFFu && i4 < (unsigned long long)p.numRays * 2) cpAsync16(ring + half * (kChunk * 32) + lane * 16, p.rays + i4);
+        cpAsyncCommit();
+    };
+    auto chunkCount = [&](unsigned base) -> int {
+        return base == 0xFFFFFFFFu ? 0 : (int)min((unsigned)kChunk, (unsigned)p.numRays - base);
+    };
+    if (FETCH == 1) {
+        headBase = claimChunk(); headCnt = chunkCount(headBase);
+        loadChunk(headBase, 0);
+        nextBase = claimChunk(); nextCnt = chunkCount(nextBase);
+        loadChunk(nextBase, 1);
+        poolEmpty = (headCnt == 0);
+    }
+
     while (true) {
         __syncwarp();
         // ---- store finished rays, refill (same scheme as trace.cu) ----------------------------
@@ -103,6 +176,32 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             storeResult(p, (unsigned)rayidx, id, hitT, hitU, hitV);
             rayidx = -1;
         }
+        if (FETCH == 1) {
+            // serve the idle lanes from the head chunk; when it runs out, step to the next one ONCE per visit (its copy was
+            // started a whole refill ago) and start the copy of the one after.  Lanes that drew a degenerate ray draw again.
+            bool stepped = false;
+            for (;;) {
+                const unsigned maskT = __ballot_sync(kFullMask, !active);
+                if (maskT == 0 || poolEmpty) break;
+                if (headPos == headCnt) {
+                    if (stepped) break;
+                    stepped = true;
+                    cpAsyncWaitAll();
+                    __syncwarp();
+                    headHalf ^= 1; headBase = nextBase; headCnt = nextCnt; headPos = 0;
+                    nextBase = claimChunk(); nextCnt = chunkCount(nextBase);
+                    loadChunk(nextBase, headHalf ^ 1);
+                    if (headCnt == 0) { poolEmpty = true; break; }
+                }
+                const int take = min((int)__popc(maskT), headCnt - headPos);
+                const int rank = __popc(maskT & ((1u << lane) - 1u));
+                if (!active && rank < take) {
+                    const unsigned a = ring + headHalf * (kChunk * 32) + (unsigned)(headPos + rank) * 32;
+                    takeRay(headBase + headPos + rank, lds128(a), lds128(a + 16));
+                }
+                headPos += take;
+            }
+        } else
         for (;;) {
             const unsigned maskT = __ballot_sync(kFullMask, !active);
             if (maskT == 0 || poolEmpty) break;
@@ -113,43 +212,24 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             base = __shfl_sync(kFullMask, base, leader);
             if (STATS && lane == leader) stFetches++;
             poolEmpty = (base + numT >= (unsigned)p.numRays);
-            bool degenerate = false;
             if (!active) {
                 const unsigned idx = base + __popc(maskT & ((1u << lane) - 1u));
                 if (idx < (unsigned)p.numRays) {
                     float4 o, d;
                     if (p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
                     else { o = ldg4(p.rays + 2 * (size_t)idx); d = ldg4(p.rays + 2 * (size_t)idx + 1); }
-                    if (d.w < o.w) {
-                        // a degenerate ray (tmax < tmin, RayGenKernels.cu:223) can hit nothing: its record is written here
-                        storeResult(p, idx, -1, d.w, 0.0f, 0.0f);
-                        degenerate = true;
-                    } else {
-                        rayidx = (int)idx;
-                        origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
-                        dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
-                        const float ooeps = 8.271806125530277e-25f;    // 2^-80 (kepler_dynamic_fetch.cu:134-137)
-                        idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-                        idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-                        idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-                        // bit set <=> the ray travels towards + on that axis; replicated into four bytes
-                        octinv4 = ((idirx < 0.0f ? 0u : 4u) | (idiry < 0.0f ? 0u : 2u) | (idirz < 0.0f ? 0u : 1u)) * 0x01010101u;
-                        G = make_uint2(0u, 0x80000000u);               // the root, as a group of one
-                        T = make_uint2(0u, 0u);
-                        sp = 0; hitIndex = -1;
-                        if (BARY) { hitU = 0.0f; hitV = 0.0f; }
-                        active = true;
-                    }
+                    takeRay(idx, o, d);
                 }
             }
-            // Secondary batches carry runs of degenerate rays (one per sample of a primary ray that missed: 52 % of the C5
-            // batch).  A fetch that brought some would leave the warp short of live lanes for a whole node step, so it is
-            // repeated until the refill threshold is met or the pool is dry.
-            if (__ballot_sync(kFullMask, degenerate) == 0) break;
-            if (p.refill && __popc(__ballot_sync(kFullMask, active)) >= p.fetchThreshold) break;
-            if (!p.refill && __ballot_sync(kFullMask, active) != 0) break;
+            // A fetch that brought only degenerate rays is repeated at once (nobody is waiting).  Repeating it until the refill
+            // threshold is met whenever SOME of the fetched rays were degenerate was measured and lost 11 % on the C5 batch
+            // (6.27 M instead of 4.64 M fetches, each a round trip the live lanes sit through): profiles/r02_explore_c5_switches.log.
+            if (__ballot_sync(kFullMask, active) != 0) break;
         }
-        if (__ballot_sync(kFullMask, active) == 0) break;              // nothing in flight and the pool is dry
+        if (__ballot_sync(kFullMask, active) == 0) {
+            if (poolEmpty) break;                                       // nothing in flight and the pool is dry
+            continue;                                                   // only degenerate rays so far: draw again
+        }
         const int threshold = poolEmpty ? 0 : p.fetchThreshold;
 
         while (active) {
@@ -309,12 +389,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, int FETCH>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>;
     int blocksPerSm = 0;
-    const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2);
+    const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2) + (FETCH ? (size_t)(BLOCK / 32) * kRingBytes : 0);
     { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
@@ -346,18 +426,18 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0>
+template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0, int FETCH = 0>
 static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS)
-        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
-                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
-    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
-                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
-    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
-                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream);
 }
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
@@ -387,25 +467,23 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
     p.streamRays = (ctx->cfg.tune & B2RT_TUNE_NO_STREAM) ? 0 : 1;
-    p.refill = (ctx->cfg.tune & B2RT_TUNE_NO_REFILL) ? 0 : 1;
     p.pushLimit = 0;
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
     switch (variant) {
     default:
+    case 108: return launchWideFlags<256, 4, 3, 1, 8>(ctx, p, flags, stream);      // <= 64 regs, 32 warps/SM; triangle groups postponed below 1/3 of the
+                                                                                   // lanes, look-ahead triangle loop, 8 stack entries in shared memory
+    case 114: return launchWideFlags<256, 4, 3, 1, 8, 1>(ctx, p, flags, stream);   // 108 with the shared-memory ray ring (FETCH == 1): batches above 4 Mi rays
+#ifdef B2RT_EXPLORE
     case 100: return launchWideFlags<256, 3, 0>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM, no postponing
-    case 101: return launchWideFlags<256, 3, 5>(ctx, p, flags, stream);   // <= 80 regs, postpone below 1/5 of the lanes
     case 102: return launchWideFlags<256, 4, 0>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM, no postponing
-    case 103: return launchWideFlags<256, 4, 5>(ctx, p, flags, stream);   // <= 64 regs, postpone below 1/5
     case 104: return launchWideFlags<256, 4, 3>(ctx, p, flags, stream);   // postpone below 1/3
-    case 105: return launchWideFlags<256, 4, 2>(ctx, p, flags, stream);   // postpone below 1/2
     case 106: return launchWideFlags<256, 4, 3, 1>(ctx, p, flags, stream);  // 104 with the look-ahead triangle loop
-    case 107: return launchWideFlags<256, 4, 0, 1>(ctx, p, flags, stream);  // 102 with the look-ahead triangle loop
-    case 108: return launchWideFlags<256, 4, 3, 1, 8>(ctx, p, flags, stream);   // 106 with 8 stack entries in shared memory
-    case 109: return launchWideFlags<256, 4, 3, 1, 12>(ctx, p, flags, stream);  // 106 with 12
-    case 110: return launchWideFlags<256, 4, 3, 1, 4>(ctx, p, flags, stream);   // 106 with 4
+    case 109: return launchWideFlags<256, 4, 3, 1, 12>(ctx, p, flags, stream);  // 106 with 12 stack entries in shared memory
     case 111: return launchWideFlags<256, 4, 0, 1, 8>(ctx, p, flags, stream);   // 108 without postponing
     case 112: return launchWideFlags<256, 4, 2, 1, 8>(ctx, p, flags, stream);   // 108, postpone below 1/2
     case 113: return launchWideFlags<512, 2, 3, 1, 8>(ctx, p, flags, stream);   // 108 in two 512-thread CTAs
+#endif
     }
 }
 

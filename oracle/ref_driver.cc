@@ -145,7 +145,8 @@ static void usage(void)
         "        [--camera-sig S | --camera-auto] [--size W H] [--camera-out F]\n"
         "        [--primary-out PREFIX]            rays via RayGen::primary -> PREFIX.rays/.slot2id\n"
         "        [--rays-in F [--any-hit]]         trace these instead of the primaries\n"
-        "        [--results-out F] [--procs P] [--limit N] [--repeat K] [--budget-s T]   BVH::trace, timed (one JSON line per repeat)\n"
+        "        [--results-out F] [--procs P] [--limit N] [--repeat K] [--budget-s T | --prim-stride S]   BVH::trace, timed (one JSON line per repeat)\n"
+        "        [--go-file F]                     after the BVH build, wait until file F exists before tracing\n"
         "        [--ao-out PREFIX --samples S --max-dist D [--sort]]   RayGen::ao batches from the primaries\n"
         "        [--trace-secondary [--secondary-closest] [--secondary-results-out F]]  time BVH::trace on the first secondary batch\n"
         "        [--sort-in F --sort-out PREFIX]   RayBuffer::mortonSort\n");
@@ -160,6 +161,8 @@ int main(int argc, char** argv)
     float alpha = 1.0e-5f, maxDist = 0.0f;
     int W = 1024, H = 768, procs = 1, samples = 1, limit = -1, repeat = 1;
     double budgetS = 0.0;
+    int primStride = 0;
+    std::string goFile;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() -> const char* { if (i + 1 >= argc) usage(); return argv[++i]; };
@@ -179,6 +182,8 @@ int main(int argc, char** argv)
         else if (a == "--limit") limit = atoi(next());
         else if (a == "--repeat") repeat = atoi(next());
         else if (a == "--budget-s") budgetS = atof(next());      /* bound the total traced time by sampling the frame */
+        else if (a == "--prim-stride") primStride = atoi(next()); /* keep every S-th 8x8 pixel block of the frame (explicit form of --budget-s) */
+        else if (a == "--go-file") goFile = next();               /* lets a caller overlap the single-threaded BVH build with its own work */
         else if (a == "--ao-out") aoOut = next();
         else if (a == "--samples") samples = atoi(next());
         else if (a == "--max-dist") maxDist = (float)atof(next());
@@ -283,7 +288,15 @@ int main(int argc, char** argv)
         }
     }
 
+    if (!goFile.empty()) {
+        fprintf(stderr, "ref_cpu: ready, waiting for %s\n", goFile.c_str());
+        while (access(goFile.c_str(), F_OK) != 0) usleep(20000);
+    }
     if (havePrimary && (!resOut.empty() || !aoOut.empty() || secTrace)) {
+        if (primStride > 1 && raysIn.empty()) {
+            strideSample(primary, primStride);
+            fprintf(stderr, "ref_cpu: every %d-th 8x8 block -> %d primary rays\n", primStride, primary.getSize());
+        } else
         if (budgetS > 0.0 && raysIn.empty()) {
             /* calibrate on a thin sample, then keep every stride-th 8x8 block of the frame */
             RayBuffer probe(primary.getSize(), true);

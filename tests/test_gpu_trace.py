@@ -40,7 +40,7 @@ def _check_closest(oracle, bvh_arrays, rays, got, ref=None, agree=ID_AGREE):
 
 
 @pytest.mark.parametrize("kind,ntris", [("blob", 20000), ("interior", 30000), ("knot", 40000), ("strands", 30000)])
-@pytest.mark.parametrize("variant", [0, 2, 8, 10])
+@pytest.mark.parametrize("variant", [1, 8, 9, 10])
 def test_primary_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     scene = b2rt.Scene.generate(kind, ntris, 20260101)
     bvh = b2rt.BVH(scene)
@@ -138,7 +138,7 @@ def test_reference_launcher_abi(b2rt, oracle, ctx):
     assert hits == int((got["id"] >= 0).sum())
 
 
-@pytest.mark.parametrize("variant", [100, 101, 102, 103, 104, 105, 106, 107, 108, 110])
+@pytest.mark.parametrize("variant", [108, 114])
 @pytest.mark.parametrize("kind,ntris", [("interior", 30000), ("strands", 30000), ("blob", 20000)])
 def test_wide_kernel_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     """The 8-wide compressed private form (csrc/trace_wide.cu): same acceptance rule as the binary kernel, and --
@@ -168,7 +168,7 @@ def test_wide_kernel_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     assert (got["id"][5::97] == -1).all() and (got["t"][5::97] == -1.0).all()
 
 
-@pytest.mark.parametrize("variant", [6, 1, 3, 9])
+@pytest.mark.parametrize("variant", [1, 9])
 @pytest.mark.parametrize("kind,ntris", [("interior", 30000), ("knot", 40000)])
 @pytest.mark.parametrize("count", [1, 37, 4097, 0])
 def test_any_hit_subtree_sharing(b2rt, oracle, ctx, kind, ntris, variant, count):
@@ -231,7 +231,7 @@ def test_wide_kernel_any_hit_and_secondary(b2rt, oracle, ctx):
     rg = b2rt.RayGen(1 << 21, ctx)
     prim = b2rt.RayBuffer()
     rg.primary(prim, origin, m, 256, 192, scene.camera["far"])
-    ctx.set_trace_config(variant=100)
+    ctx.set_trace_config(variant=108)
     try:
         tracer.traceBatch(prim)
         sec = b2rt.RayBuffer()
@@ -348,7 +348,7 @@ def test_traces_on_two_streams_overlap_safely(b2rt, oracle, ctx):
                 assert same.mean() >= 0.999 and (got["t"][same] == want["t"][same]).all()
 
 
-@pytest.mark.parametrize("pair", [(6, 8), (1, 10), (7, 9)])
+@pytest.mark.parametrize("pair", [(1, 10)])
 def test_lookahead_leaf_loop_returns_the_same_bits(b2rt, oracle, ctx, pair):
     """LEAF = 1 (row 0 of the next triangle requested ahead, Woop test without early-outs; trace.cu) performs the same
     floating-point operations in the same order as the reference-shaped loop: wherever both kernels report the same

@@ -16,7 +16,7 @@ wl = importlib.import_module("gpu-ray-tracing_b200.workloads")
 
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "c2"
-    variants = [int(v) for v in sys.argv[2:]] or [8, 6, 1]
+    variants = [int(v) for v in sys.argv[2:]] or [8, 1]
     ctx = b2rt.Context.get(0)
     scene, bvh = wl.build_scene_and_bvh(name, log=lambda s: print(s, flush=True))
     frame = wl.Frame(name, scene, bvh.arrays(), "cuda:0", ctx)

@@ -7,12 +7,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 b2rt = importlib.import_module("gpu-ray-tracing_b200")
 wl = importlib.import_module("gpu-ray-tracing_b200.workloads")
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 300
-variants = [int(v) for v in (sys.argv[2] if len(sys.argv) > 2 else "9,6,1,7,3").split(",")]
+variants = [int(v) for v in (sys.argv[2] if len(sys.argv) > 2 else "9,1").split(",")]
 ctx = b2rt.Context.get(0)
 scene, bvh = wl.build_scene_and_bvh("c3", log=print)
 frame = wl.Frame("c3", scene, bvh.arrays(), "cuda:0", ctx)
 reference = []
-ctx.set_trace_config(variant=2)
+ctx.set_trace_config(variant=1)
 for rb, _ in frame.batches:
     frame.tracer.traceBatch(rb)
     reference.append((rb.m_results[:rb.getSize(), 0] >= 0).clone())
