@@ -416,7 +416,7 @@ def product_arm(args):
     b2rt = importlib.import_module(PKG)
     wl = importlib.import_module(PKG + ".workloads")
     mg = importlib.import_module(PKG + ".multigpu")
-    mg.bind_to_local_cores(local_rank, ws)          # before any pinned allocation: first-touch decides the NUMA node
+    binding = mg.bind_to_local_cores(local_rank, ws)          # before any pinned allocation: first-touch decides the NUMA node
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     if ws > 1:
@@ -624,7 +624,8 @@ def product_arm(args):
                    "bvh": "%d nodes, %d Woop rows" % (arrays["nodes"].size // 16, arrays["woop"].size // 4)},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
                 "steps": e2e_steps, "ms_per_step": e2e_ms_max / e2e_steps,
-                "api": "b2rt_trace_host_begin per batch + b2rt_trace_host_end per step (pinned host rays in, host hit records out)"},
+                "api": "b2rt_trace_host_begin per batch + b2rt_trace_host_end per step (pinned host rays in, host hit records out)",
+                "host_binding": binding},
         "gpu_launches": int(launches_all),
         "wall_s_timed_region": t_wall,
         "clocks": clocks,

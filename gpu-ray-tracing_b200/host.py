@@ -484,8 +484,16 @@ class CudaTracer:
         if bvh.getLayout() != self.getDesiredBVHLayout():
             return      # reported at traceBatch, like the reference
         n, w, t = bvh.getNodeBuffer_dev(), bvh.getTriWoopBuffer_dev(), bvh.getTriIndexBuffer_dev()
+        # In the reference this is a pointer assignment and Renderer::beginFrame does it every frame (Renderer.cc:116); here
+        # b2rt_set_bvh builds private copies (re-laid nodes, on first use the 8-wide form), so the same CudaBVH object bound
+        # again is not uploaded again.  One BVH per context: the last one bound is the one every tracer of the device traces.
+        key = (id(bvh), n.data_ptr(), n.numel(), w.data_ptr(), w.numel(), t.data_ptr(), t.numel())
+        if getattr(self._ctx, "_bound_bvh", None) == key:
+            return
         check(lib().b2rt_set_bvh(self._ctx.handle, _dptr(n), n.numel() * 4, _dptr(w), w.numel() * 4, _dptr(t),
                                  t.numel() * 4, bvh.getLayout(), 1), self._ctx.handle)
+        self._ctx._bound_bvh = key
+        self._ctx._bound_bvh_ref = bvh          # keeps id(bvh) from being reused while it is the bound one
 
     def traceBatch(self, rays):
         """CudaTracer::traceBatch (CudaTracer.cc:119-178): returns the kernel time in MILLISECONDS

@@ -88,3 +88,60 @@ def reduce_stats(values, device, op="sum"):
     t = torch.tensor(values, dtype=torch.float64, device=_comm_device(device))
     dist.all_reduce(t, dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX)
     return t.tolist()
+
+
+def max_over_ranks(value, device):
+    return int(reduce_stats([float(value)], device, op="max")[0])
+
+
+def all_sizes(value, device):
+    """The integer `value` of every rank, in rank order."""
+    rank, ws = world()
+    if ws == 1:
+        return [int(value)]
+    t = torch.zeros(ws, dtype=torch.float64, device=_comm_device(device))
+    t[rank] = float(value)
+    dist.all_reduce(t, dist.ReduceOp.SUM)
+    return [int(v) for v in t.tolist()]
+
+
+def local_core_slice(cores, local_rank, local_world):
+    """The share of the allowed host cores that rank `local_rank` of `local_world` ranks on this node keeps: a contiguous
+    block, every core in exactly one block, sizes differ by at most one.  With fewer cores than ranks everybody keeps all."""
+    cores = sorted(cores)
+    if local_world <= 1 or len(cores) < local_world:
+        return cores
+    lo, hi = shard_range(len(cores), local_rank, local_world)
+    return cores[lo:hi]
+
+
+def bind_to_local_cores(local_rank, local_world):
+    """Pin this process to its GPU's NUMA-local host cores, and inside them to its own block, BEFORE it allocates pinned
+    memory: cudaHostAlloc pages are first-touched by the calling thread, so they land on the NUMA node it runs on, and the
+    runtime's copy-submission threads of eight ranks no longer share cores.  (Round 1: end-to-end throughput through host
+    buffers scaled 1 -> 2.15x at 8 GPUs with every rank free to run anywhere.)  Returns a description for the bench line."""
+    import os
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+    except Exception:
+        return {"bound": False, "why": "no sched_getaffinity"}
+    local = allowed
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[local_rank]) if vis else local_rank
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = (max(allowed) // 64) + 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        near = [c for c in allowed if (mask[c // 64] >> (c % 64)) & 1]
+        if near:
+            local = near
+    except Exception:
+        pass
+    mine = local_core_slice(local, local_rank, local_world)
+    try:
+        os.sched_setaffinity(0, mine)
+    except Exception as e:
+        return {"bound": False, "why": str(e)}
+    return {"bound": True, "cores": len(mine), "first": mine[0], "last": mine[-1], "gpu_local_cores": len(local)}

@@ -38,6 +38,20 @@ def describe(name):
         " x%d" % c["samples"] if c["ray_type"] != "primary" else "", ", Morton-sorted" if c["sort"] else "")
 
 
+def describe_step(name):
+    """What one bench step traces (identical text in both arms of bench.py)."""
+    c = CONFIGS[name]
+    if c.get("total_rays"):
+        return "closest-hit trace of one %d-ray diffuse batch (%d samples per primary hit; degenerate rays of primary misses launched, not counted)" % (
+            c["total_rays"], c["samples"])
+    if c["ray_type"] == "primary":
+        return "closest-hit trace of the frame's primary batch"
+    kind = "closest-hit" if c["ray_type"] == "diffuse" else "any-hit"
+    return "%s%s trace of the frame's %s batches (%d samples per primary hit)%s" % (
+        "closest-hit trace of the primary batch + " if c.get("with_primary") else "", kind, c["ray_type"], c["samples"],
+        ", each Morton-sorted first (untimed)" if c["sort"] else "")
+
+
 def build_scene_and_bvh(name, use_cache=True, log=None):
     """Scene + host BVH for a config; the BVH goes through a bvhcache file (Renderer.cc:176-211)."""
     c = CONFIGS[name]
@@ -196,3 +210,64 @@ def _slice_buffer(rb, lo, hi, closest=None):
     out.m_IDToSlot[:n].copy_(ar)
     out.m_slotToID[:n].copy_(ar)
     return out
+
+
+def render_frame_e2e(name, scene, cuda_bvh, ctx, device, steps=3, shard=(0, 1)):
+    """The reference's real frame, end to end (Renderer::beginFrame / nextBatch / traceBatch / reconstruct,
+    Renderer.cc:112-152,242-300): camera -> primary rays generated on the device -> closest-hit trace -> hit count ->
+    diffuse batches of at most 2 Mi rays generated on the device from the primary hits -> closest-hit trace -> reconstruct
+    -> the frame's pixels copied to the host.  Nothing but the camera goes up; pixels and one counter come down.
+    With shard = (rank, world) this rank renders every world-th 8x8 pixel block.  Wall clock, device idle at both ends."""
+    from .host import reconstruct
+    c = CONFIGS[name]
+    w, h = c["size"]
+    samples = c["samples"]
+    device = torch.device(device)
+    rank, ws = shard
+    tracer = CudaTracer(ctx)
+    tracer.setBVH(cuda_bvh)
+    raygen = RayGen(1 << 21, ctx)                       # Renderer.cc:46
+    origin, m = camera_matrices(scene.camera, w, h)
+    far = scene.camera["far"]
+    prim = RayBuffer(0, True, device)
+    sec = RayBuffer(0, True, device)
+    ntri = scene.getNumTriangles()
+    material = torch.full((ntri,), 0xFF808080, dtype=torch.int64, device=device).to(torch.int32)
+    shaded = torch.full((ntri,), 0xFFC0C0C0, dtype=torch.int64, device=device).to(torch.int32)
+    pixels = torch.zeros(w * h, dtype=torch.int32, device=device)
+    host_pixels = torch.empty(w * h, dtype=torch.int32).pin_memory()
+    mine = None
+    if ws > 1:
+        idx = torch.arange(w * h, device=device)
+        mine = idx[((idx // 64) % ws) == rank]
+    times, counted, launches = [], 0, 0
+    for step in range(steps + 1):                        # the first pass warms up
+        torch.cuda.synchronize()
+        l0 = ctx.launch_count()
+        t0 = time.perf_counter()
+        raygen.primary(prim, origin, m, w, h, far)
+        src = prim
+        if mine is not None:
+            src = _gather_buffer(prim, mine)
+            src.m_slotToID[:src.getSize()].copy_(prim.m_slotToID[mine])
+        tracer.traceBatchAsync(src)
+        hits = countHits(src.getResultBuffer_dev(), ctx)                       # Renderer::getTotalNumRays (Renderer.cc:221-238)
+        newBatch, first = True, 0
+        while True:
+            cont, newBatch = raygen.ao(sec, src, scene, samples, far, newBatch)
+            if not cont:
+                break
+            sec.setNeedClosestHit(True)                                         # Renderer.cc:277
+            tracer.traceBatchAsync(sec)
+            n_prim = sec.getSize() // samples
+            reconstruct("diffuse", samples, first, n_prim, src, sec, material, shaded, pixels, ctx)
+            first += n_prim
+        host_pixels.copy_(pixels, non_blocking=True)
+        torch.cuda.synchronize()
+        if step:
+            times.append((time.perf_counter() - t0) * 1e3)
+            counted = hits * samples
+            launches = ctx.launch_count() - l0
+    return {"ms_per_step": float(np.median(times)), "counted": int(counted), "h2d": 19 * 4, "d2h": w * h * 4 // ws + 8, "launches": int(launches),
+            "api": "RayGen::primary -> traceBatch -> countHits -> {RayGen::ao (diffuse, 2 Mi-ray batches) -> traceBatch -> reconstruct} -> pixels to the host; "
+                   "wall clock per frame, median of %d" % len(times)}
