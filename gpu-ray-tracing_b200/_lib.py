@@ -12,7 +12,7 @@ LAYOUT_COMPACT2 = 5
 TRACE_ANY_HIT = 1
 TRACE_WRITE_BARY = 2
 TRACE_STATS = 4
-TUNE_NO_STREAM, TUNE_NO_RING, TUNE_GREEDY_WIDE, TUNE_L2_WINDOW = 1, 2, 4, 8
+TUNE_NO_STREAM, TUNE_GREEDY_WIDE, TUNE_L2_WINDOW = 1, 4, 8
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmin", "<f4"), ("d", "<f4", 3), ("tmax", "<f4")])
 RESULT_DTYPE = np.dtype([("id", "<i4"), ("t", "<f4"), ("padA", "<i4"), ("padB", "<i4")])

@@ -150,6 +150,37 @@ __device__ __forceinline__ float rcp_approx(float x)
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+// The Woop test's arithmetic, instruction for instruction what nvcc makes of kepler_dynamic_fetch.cu:336-358 in the reference's
+// build (--use_fast_math: flush-to-zero FFMA / FMUL / FADD, MUFU.RCP; SASS of that file compiled for sm_100a, excerpt in
+// profiles/r02_sass_woop_reference_vs_b2rt.md):
+//   Oz    = fma(-oz, r0.z, fma(-oy, r0.y, fma(-ox, r0.x, r0.w)))
+//   denom = fma( dz, r0.z, fma( dx, r0.x, dy * r0.y))          <- the PRODUCT is the y term: nvcc re-associates the sum
+//   t     = Oz * rcp(denom)
+//   Ox    = fma( oz, r1.z, fma( oy, r1.y, fma( ox, r1.x, r1.w))),  Dx = fma(dz, r1.z, fma(dx, r1.x, dy * r1.y)),  u = fma(t, Dx, Ox)
+// (v likewise with row 2).  With the same operations in the same order t, u and v are bit-identical to the reference kernel's
+// for the same ray and triangle; round 1 had the product on the x term and differed from it by up to 2.9e-5 relative on rays
+// whose Oz cancels (secondary rays starting next to the plane they hit).
+__device__ __forceinline__ float ffmaFtz(float a, float b, float c)
+{
+    float r;
+    asm("fma.rn.ftz.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float fmulFtz(float a, float b)
+{
+    float r;
+    asm("mul.rn.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float faddFtz(float a, float b)
+{
+    float r;
+    asm("add.rn.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float woopDot(float dx, float dy, float dz, const float4 r) { return ffmaFtz(dz, r.z, ffmaFtz(dx, r.x, fmulFtz(dy, r.y))); }
+__device__ __forceinline__ float woopPlane(float ox, float oy, float oz, const float4 r) { return ffmaFtz(oz, r.z, ffmaFtz(oy, r.y, ffmaFtz(ox, r.x, r.w))); }
+
 // shared-memory loads through a 32-bit shared-window address (read-only data staged before a barrier)
 __device__ __forceinline__ float4 lds128(unsigned addr)
 {

@@ -388,16 +388,16 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                         const float4 n00 = ldg4(p.woop + triAddr + 3);
                         const float4 v11 = ldg4(p.woop + triAddr + 1), v22 = ldg4(p.woop + triAddr + 2);
                         if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
-                        const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
-                        const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
-                        const float t = __fmul_rn(Oz, invDz);
-                        const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
-                        const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
-                        const float u = __fmaf_rn(t, Dx, Ox);
-                        const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
-                        const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
-                        const float v = __fmaf_rn(t, Dy, Oy);
-                        if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                        const float Oz = woopPlane(-origx, -origy, -origz, v00);
+                        const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
+                        const float t = fmulFtz(Oz, invDz);
+                        const float Ox = woopPlane(origx, origy, origz, v11);
+                        const float Dx = woopDot(dirx, diry, dirz, v11);
+                        const float u = ffmaFtz(t, Dx, Ox);
+                        const float Oy = woopPlane(origx, origy, origz, v22);
+                        const float Dy = woopDot(dirx, diry, dirz, v22);
+                        const float v = ffmaFtz(t, Dy, Oy);
+                        if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && faddFtz(u, v) <= 1.0f) {
                             hitT = t; hitIndex = triAddr;
                             if (BARY) { hitU = u; hitV = v; }
                             if (ANY_HIT) { nodeAddr = kSentinel; break; }
@@ -410,18 +410,18 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                         if (__float_as_int(v00.x) == (int)0x80000000) break;       // leaf terminator
                         if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
 
-                        const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
-                        const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
-                        const float t = __fmul_rn(Oz, invDz);
+                        const float Oz = woopPlane(-origx, -origy, -origz, v00);
+                        const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
+                        const float t = fmulFtz(Oz, invDz);
                         if (t > tmin && t < hitT) {
-                            const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
-                            const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
-                            const float u = __fmaf_rn(t, Dx, Ox);
+                            const float Ox = woopPlane(origx, origy, origz, v11);
+                            const float Dx = woopDot(dirx, diry, dirz, v11);
+                            const float u = ffmaFtz(t, Dx, Ox);
                             if (u >= 0.0f) {
-                                const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
-                                const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
-                                const float v = __fmaf_rn(t, Dy, Oy);
-                                if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                                const float Oy = woopPlane(origx, origy, origz, v22);
+                                const float Dy = woopDot(dirx, diry, dirz, v22);
+                                const float v = ffmaFtz(t, Dy, Oy);
+                                if (v >= 0.0f && faddFtz(u, v) <= 1.0f) {
                                     hitT = t; hitIndex = triAddr;
                                     if (BARY) { hitU = u; hitV = v; }
                                     if (ANY_HIT) { nodeAddr = kSentinel; break; }
@@ -460,12 +460,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                 if (BARY) {
                     const float4 o = ldg4(p.rays + 2 * (size_t)r);
                     const float4 v11 = ldg4(p.woop + row + 1), v22 = ldg4(p.woop + row + 2);
-                    const float Ox = __fmaf_rn(o.z, v11.z, __fmaf_rn(o.y, v11.y, __fmaf_rn(o.x, v11.x, v11.w)));
-                    const float Dx = __fmaf_rn(d.z, v11.z, __fmaf_rn(d.y, v11.y, __fmul_rn(d.x, v11.x)));
-                    u = __fmaf_rn(t, Dx, Ox);
-                    const float Oy = __fmaf_rn(o.z, v22.z, __fmaf_rn(o.y, v22.y, __fmaf_rn(o.x, v22.x, v22.w)));
-                    const float Dy = __fmaf_rn(d.z, v22.z, __fmaf_rn(d.y, v22.y, __fmul_rn(d.x, v22.x)));
-                    v = __fmaf_rn(t, Dy, Oy);
+                    u = ffmaFtz(t, woopDot(d.x, d.y, d.z, v11), woopPlane(o.x, o.y, o.z, v11));
+                    v = ffmaFtz(t, woopDot(d.x, d.y, d.z, v22), woopPlane(o.x, o.y, o.z, v22));
                 }
             }
             if (BARY) p.results[r] = make_int4(id, __float_as_int(t), __float_as_int(u), __float_as_int(v));
@@ -602,8 +598,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
             // ... unless the collapsed tree is too deep for that kernel's stack (a degenerate caller-built BVH): stay binary
             const int rc = ensureWide(ctx);
             if (rc) return rc;
-            if (ctx->wideMaxDepth <= kWideMaxDepth)
-                variant = (numRays > (4 << 20) && !(ctx->cfg.tune & B2RT_TUNE_NO_RING)) ? 114 : 108;
+            if (ctx->wideMaxDepth <= kWideMaxDepth) variant = 108;
         }
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);
@@ -684,18 +679,18 @@ __global__ void __launch_bounds__(256) countWorkKernel(const float4* __restrict_
                     cT++;
                     const float Oz = __fmaf_rn(-o.z, v00.z, __fmaf_rn(-o.y, v00.y, __fmaf_rn(-o.x, v00.x, v00.w)));
                     const float invDz = __fdiv_rn(1.0f, __fmaf_rn(d.z, v00.z, __fmaf_rn(d.y, v00.y, __fmul_rn(d.x, v00.x))));
-                    const float t = __fmul_rn(Oz, invDz);
+                    const float t = fmulFtz(Oz, invDz);
                     if (t > tmin && t < hitT) {
                         cU++;
                         const float Ox = __fmaf_rn(o.z, v11.z, __fmaf_rn(o.y, v11.y, __fmaf_rn(o.x, v11.x, v11.w)));
                         const float Dx = __fmaf_rn(d.z, v11.z, __fmaf_rn(d.y, v11.y, __fmul_rn(d.x, v11.x)));
-                        const float u = __fmaf_rn(t, Dx, Ox);
+                        const float u = ffmaFtz(t, Dx, Ox);
                         if (u >= 0.0f) {
                             cV++;
                             const float Oy = __fmaf_rn(o.z, v22.z, __fmaf_rn(o.y, v22.y, __fmaf_rn(o.x, v22.x, v22.w)));
                             const float Dy = __fmaf_rn(d.z, v22.z, __fmaf_rn(d.y, v22.y, __fmul_rn(d.x, v22.x)));
-                            const float v = __fmaf_rn(t, Dy, Oy);
-                            if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                            const float v = ffmaFtz(t, Dy, Oy);
+                            if (v >= 0.0f && faddFtz(u, v) <= 1.0f) {
                                 hitT = t; hitIndex = triAddr;
                                 if (anyHit) { done = true; break; }
                             }

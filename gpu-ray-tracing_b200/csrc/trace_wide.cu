@@ -64,26 +64,13 @@ __device__ __forceinline__ void storeResultT(const WideParams& p, unsigned rayid
     }
 }
 
-// FETCH == 1: rays reach a warp through a private two-chunk ring in shared memory instead of one atomic + one dependent global
-// load per refill.  ncu on the C5 batch: a warp refills 980 times per launch and every refill is a chain of an atomic on the
-// work counter (~1 us under load) and the ray load behind it (DRAM: the batch streams through once) during which the
-// warp's 20-odd live lanes wait -- a sixth of every warp's time.  Here chunks of kChunk rays are dealt out STATICALLY for the
-// first 7/8 of the batch (chunk r * warps + w goes to warp w in its round r: no atomic, the address of the chunk after next is
-// known, so it is copied into the ring with cp.async one refill ahead) and claimed from the work counter only for the last
-// eighth, which evens out what the static deal left unbalanced.  A refill then costs two shared-memory loads per lane.
-// Chosen for batches above 4 Mi rays only (launchTrace): a warp holds up to two chunks it has not started, which would
-// lengthen the tail of a frame-sized launch.
-constexpr int kChunk = 16;              // rays per chunk: the mean refill of the on-demand scheme is 14.5 rays
-constexpr int kRingBytes = 2 * kChunk * 32;     // per warp: two chunks of 32-byte rays
-
-__device__ __forceinline__ void cpAsync16(unsigned dstShared, const void* src)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dstShared), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cpAsyncWaitAll() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, int FETCH>
+// Measured and removed (round 2, profiles/r02_explore_c5_ring.log, r02_ncu_trace_wide_c5_ring.md): rays dealt out statically in
+// 16-ray chunks through a per-warp shared-memory ring filled by cp.async one refill ahead, the work counter only for the last
+// eighth of the batch.  It does what it was built for -- long_scoreboard stalls per issue fall from 2.78 to 1.39: half of them
+// are the refill's atomic -> ray-load chain -- but a chunk is 16 samples of ONE primary ray, so 52 % of the C5 chunks are
+// entirely degenerate and a refill often fills no lane: 20 % more instructions, 40 % instead of 50 % of the warp slots
+// occupied, 3 265 -> 2 380 Mrays/s.
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
     auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
@@ -132,42 +119,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         active = true;
     };
 
-    // FETCH == 1: the warp's ring and its place in the deal (all warp-uniform)
-    const unsigned ring = (unsigned)__cvta_generic_to_shared(s_wideStack) + (unsigned)(SSLOTS * BLOCK * sizeof(uint2)) +
-                          (unsigned)(threadIdx.x >> 5) * kRingBytes;
-    const unsigned numWarps = gridDim.x * (BLOCK / 32), warpId = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
-    const unsigned numChunks = ((unsigned)p.numRays + kChunk - 1) / kChunk;
-    const unsigned staticRounds = (numChunks / numWarps) - (numChunks / numWarps) / 8;
-    unsigned round = 0, headBase = 0, nextBase = 0;
-    int headCnt = 0, headPos = 0, nextCnt = 0, headHalf = 0;
-    auto claimChunk = [&]() -> unsigned {           // first ray of the warp's next chunk, 0xFFFFFFFF when the batch is dealt out
-        unsigned c;
-        if (round < staticRounds) c = round * numWarps + warpId;
-        else {
-            unsigned v = 0;
-            if (lane == 0) v = (unsigned)atomicAdd(p.warpCounter, 1);
-            c = staticRounds * numWarps + __shfl_sync(kFullMask, v, 0);
-            if (STATS && lane == 0) stFetches++;
-        }
-        round++;
-        return c < numChunks ? c * kChunk : 0xFFFFFFFFu;
-    };
-    auto loadChunk = [&](unsigned base, int half) {     // asynchronous copy of a chunk into one half of the ring
-        const unsigned long long i4 = (unsigned long long)base * 2 + lane;       // kChunk rays = 32 float4: one per lane
-        if (base != 0xFFFFFFFFu && i4 < (unsigned long long)p.numRays * 2) cpAsync16(ring + half * (kChunk * 32) + lane * 16, p.rays + i4);
-        cpAsyncCommit();
-    };
-    auto chunkCount = [&](unsigned base) -> int {
-        return base == 0xFFFFFFFFu ? 0 : (int)min((unsigned)kChunk, (unsigned)p.numRays - base);
-    };
-    if (FETCH == 1) {
-        headBase = claimChunk(); headCnt = chunkCount(headBase);
-        loadChunk(headBase, 0);
-        nextBase = claimChunk(); nextCnt = chunkCount(nextBase);
-        loadChunk(nextBase, 1);
-        poolEmpty = (headCnt == 0);
-    }
-
     while (true) {
         __syncwarp();
         // ---- store finished rays, refill (same scheme as trace.cu) ----------------------------
@@ -176,32 +127,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             storeResult(p, (unsigned)rayidx, id, hitT, hitU, hitV);
             rayidx = -1;
         }
-        if (FETCH == 1) {
-            // serve the idle lanes from the head chunk; when it runs out, step to the next one ONCE per visit (its copy was
-            // started a whole refill ago) and start the copy of the one after.  Lanes that drew a degenerate ray draw again.
-            bool stepped = false;
-            for (;;) {
-                const unsigned maskT = __ballot_sync(kFullMask, !active);
-                if (maskT == 0 || poolEmpty) break;
-                if (headPos == headCnt) {
-                    if (stepped) break;
-                    stepped = true;
-                    cpAsyncWaitAll();
-                    __syncwarp();
-                    headHalf ^= 1; headBase = nextBase; headCnt = nextCnt; headPos = 0;
-                    nextBase = claimChunk(); nextCnt = chunkCount(nextBase);
-                    loadChunk(nextBase, headHalf ^ 1);
-                    if (headCnt == 0) { poolEmpty = true; break; }
-                }
-                const int take = min((int)__popc(maskT), headCnt - headPos);
-                const int rank = __popc(maskT & ((1u << lane) - 1u));
-                if (!active && rank < take) {
-                    const unsigned a = ring + headHalf * (kChunk * 32) + (unsigned)(headPos + rank) * 32;
-                    takeRay(headBase + headPos + rank, lds128(a), lds128(a + 16));
-                }
-                headPos += take;
-            }
-        } else
         for (;;) {
             const unsigned maskT = __ballot_sync(kFullMask, !active);
             if (maskT == 0 || poolEmpty) break;
@@ -312,16 +237,16 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                     const float4* w = p.woop + (size_t)tri * 3;
                     const float4 n00 = ldg4(p.woop + (size_t)ntri * 3);
                     const float4 v11 = ldg4(w + 1), v22 = ldg4(w + 2);
-                    const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
-                    const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
-                    const float t = __fmul_rn(Oz, invDz);
-                    const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
-                    const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
-                    const float u = __fmaf_rn(t, Dx, Ox);
-                    const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
-                    const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
-                    const float v = __fmaf_rn(t, Dy, Oy);
-                    if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                    const float Oz = woopPlane(-origx, -origy, -origz, v00);
+                    const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
+                    const float t = fmulFtz(Oz, invDz);
+                    const float Ox = woopPlane(origx, origy, origz, v11);
+                    const float Dx = woopDot(dirx, diry, dirz, v11);
+                    const float u = ffmaFtz(t, Dx, Ox);
+                    const float Oy = woopPlane(origx, origy, origz, v22);
+                    const float Dy = woopDot(dirx, diry, dirz, v22);
+                    const float v = ffmaFtz(t, Dy, Oy);
+                    if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && faddFtz(u, v) <= 1.0f) {
                         hitT = t; hitIndex = tri;
                         if (BARY) { hitU = u; hitV = v; }
                         if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; }
@@ -341,18 +266,18 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 const float4* w = p.woop + (size_t)tri * 3;
                 const float4 v00 = ldg4(w), v11 = ldg4(w + 1), v22 = ldg4(w + 2);
                 // Woop test, same operation order as trace.cu (kepler_dynamic_fetch.cu:336-379)
-                const float Oz = __fmaf_rn(-origz, v00.z, __fmaf_rn(-origy, v00.y, __fmaf_rn(-origx, v00.x, v00.w)));
-                const float invDz = rcp_approx(__fmaf_rn(dirz, v00.z, __fmaf_rn(diry, v00.y, __fmul_rn(dirx, v00.x))));
-                const float t = __fmul_rn(Oz, invDz);
+                const float Oz = woopPlane(-origx, -origy, -origz, v00);
+                const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
+                const float t = fmulFtz(Oz, invDz);
                 if (t > tmin && t < hitT) {
-                    const float Ox = __fmaf_rn(origz, v11.z, __fmaf_rn(origy, v11.y, __fmaf_rn(origx, v11.x, v11.w)));
-                    const float Dx = __fmaf_rn(dirz, v11.z, __fmaf_rn(diry, v11.y, __fmul_rn(dirx, v11.x)));
-                    const float u = __fmaf_rn(t, Dx, Ox);
+                    const float Ox = woopPlane(origx, origy, origz, v11);
+                    const float Dx = woopDot(dirx, diry, dirz, v11);
+                    const float u = ffmaFtz(t, Dx, Ox);
                     if (u >= 0.0f) {
-                        const float Oy = __fmaf_rn(origz, v22.z, __fmaf_rn(origy, v22.y, __fmaf_rn(origx, v22.x, v22.w)));
-                        const float Dy = __fmaf_rn(dirz, v22.z, __fmaf_rn(diry, v22.y, __fmul_rn(dirx, v22.x)));
-                        const float v = __fmaf_rn(t, Dy, Oy);
-                        if (v >= 0.0f && __fadd_rn(u, v) <= 1.0f) {
+                        const float Oy = woopPlane(origx, origy, origz, v22);
+                        const float Dy = woopDot(dirx, diry, dirz, v22);
+                        const float v = ffmaFtz(t, Dy, Oy);
+                        if (v >= 0.0f && faddFtz(u, v) <= 1.0f) {
                             hitT = t; hitIndex = tri;
                             if (BARY) { hitU = u; hitV = v; }
                             if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; }
@@ -389,12 +314,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, int FETCH>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>;
     int blocksPerSm = 0;
-    const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2) + (FETCH ? (size_t)(BLOCK / 32) * kRingBytes : 0);
+    const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2);
     { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
@@ -426,18 +351,18 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0, int FETCH = 0>
+template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0>
 static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_STATS)
-        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream)
-                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream);
-    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream)
-                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream);
-    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream)
-                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, FETCH>(ctx, p, stream);
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
 }
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
@@ -473,7 +398,6 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     default:
     case 108: return launchWideFlags<256, 4, 3, 1, 8>(ctx, p, flags, stream);      // <= 64 regs, 32 warps/SM; triangle groups postponed below 1/3 of the
                                                                                    // lanes, look-ahead triangle loop, 8 stack entries in shared memory
-    case 114: return launchWideFlags<256, 4, 3, 1, 8, 1>(ctx, p, flags, stream);   // 108 with the shared-memory ray ring (FETCH == 1): batches above 4 Mi rays
 #ifdef B2RT_EXPLORE
     case 100: return launchWideFlags<256, 3, 0>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM, no postponing
     case 102: return launchWideFlags<256, 4, 0>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM, no postponing

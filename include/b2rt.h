@@ -69,7 +69,6 @@ typedef struct {
     unsigned tune;              /* B2RT_TUNE_* bits that switch single design decisions OFF for A/B measurements; 0 = as shipped */
 } b2rt_trace_config;
 #define B2RT_TUNE_NO_STREAM      1u  /* rays / records through the normal cache policy instead of evict-first (ld.cs / st.cs) */
-#define B2RT_TUNE_NO_RING        2u  /* 8-wide kernel, batches above 4 Mi rays: on-demand ray fetch instead of the shared-memory ray ring */
 #define B2RT_TUNE_GREEDY_WIDE    4u  /* 8-wide form: round-1 greedy top-down collapse instead of the SAH-optimal one; takes effect
                                         at the next b2rt_set_bvh */
 #define B2RT_TUNE_L2_WINDOW      8u  /* (opt-in) 8-wide kernel: persisting-L2 access window over the private wide arrays when they fit

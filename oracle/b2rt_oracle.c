@@ -582,7 +582,9 @@ void b2o_trace_mt(const float* nodes, const float* woop, const int32_t* triIndex
  * Scalar restatement of the GPU tracer -- src/rt/kernels/kepler_dynamic_fetch.cu:
  * ray setup :123-140, node test :213-285, Woop test :328-381, result :407-408.
  * Canonical order: no speculation, no postponement (neither changes the result of a
- * closest-hit query).  fmaf marks the products nvcc contracts (-fmad=true, the reference build).
+ * closest-hit query).  fmaf marks the products nvcc contracts (-fmad=true, the reference build); in the
+ * three direction sums dx*x + dy*y + dz*z the plain product is the y term, as in the SASS of the reference
+ * kernel built here (oracle/_ref/libref_gpu.so: FMUL dy*y, FFMA dx*x, FFMA dz*z -- fast-math re-association).
  * spanBegin/EndKepler (CudaTracerKernels.hh:274-275) are decision-identical to fminf/fmaxf
  * for tmin >= 0; plain float min/max is used here.
  * ---------------------------------------------------------------------------------------- */
@@ -646,17 +648,17 @@ void b2o_trace_woop(const float* nodes, const float* woop, const int32_t* triInd
                     const float* v22 = v00 + 8;
                     if (ctr) ctr->tris++;
                     float Oz = fmaf(-origz, v00[2], fmaf(-origy, v00[1], fmaf(-origx, v00[0], v00[3])));
-                    float invDz = 1.0f / fmaf(dirz, v00[2], fmaf(diry, v00[1], dirx * v00[0]));
+                    float invDz = 1.0f / fmaf(dirz, v00[2], fmaf(dirx, v00[0], diry * v00[1]));
                     float t = Oz * invDz;
                     if (t > tmin && t < hitT) {
                         if (ctr) ctr->ustage++;
                         float Ox = fmaf(origz, v11[2], fmaf(origy, v11[1], fmaf(origx, v11[0], v11[3])));
-                        float Dx = fmaf(dirz, v11[2], fmaf(diry, v11[1], dirx * v11[0]));
+                        float Dx = fmaf(dirz, v11[2], fmaf(dirx, v11[0], diry * v11[1]));
                         float u = fmaf(t, Dx, Ox);
                         if (u >= 0.0f) {
                             if (ctr) ctr->vstage++;
                             float Oy = fmaf(origz, v22[2], fmaf(origy, v22[1], fmaf(origx, v22[0], v22[3])));
-                            float Dy = fmaf(dirz, v22[2], fmaf(diry, v22[1], dirx * v22[0]));
+                            float Dy = fmaf(dirz, v22[2], fmaf(dirx, v22[0], diry * v22[1]));
                             float v = fmaf(t, Dy, Oy);
                             if (v >= 0.0f && u + v <= 1.0f) {
                                 hitT = t; hitIndex = triAddr; hitU = u; hitV = v;
