@@ -263,6 +263,10 @@ int main(int argc, char** argv)
         writeFile(camOut, buf, sizeof(buf));
     }
 
+    if (!goFile.empty()) {
+        fprintf(stderr, "ref_cpu: ready, waiting for %s\n", goFile.c_str());
+        while (access(goFile.c_str(), F_OK) != 0) usleep(20000);
+    }
     RayGen raygen(1 << 21);       /* Renderer.cc:46 */
     RayBuffer primary;
     bool havePrimary = false;
@@ -288,10 +292,6 @@ int main(int argc, char** argv)
         }
     }
 
-    if (!goFile.empty()) {
-        fprintf(stderr, "ref_cpu: ready, waiting for %s\n", goFile.c_str());
-        while (access(goFile.c_str(), F_OK) != 0) usleep(20000);
-    }
     if (havePrimary && (!resOut.empty() || !aoOut.empty() || secTrace)) {
         if (primStride > 1 && raysIn.empty()) {
             strideSample(primary, primStride);

@@ -1,0 +1,238 @@
+"""Parity at BASELINE.json's full sizes against BOTH of the reference's tracers, with the north_star's numbers
+(tests/parity_util.py: >= 99.99 % identical ids, t within 1e-5 relative on equal ids, every mismatch classified from the mesh):
+
+  (a) the reference's CUDA kernel (oracle/_ref/libref_gpu.so = kepler_dynamic_fetch.cu built for sm_100a) on the same device
+      arrays and rays -- C2 (both batches), C4 (primary + diffuse, 6.5 M triangles), C5 (the whole 64 Mi-ray batch with the
+      shipped default, an 8 Mi-ray slice with the binary kernel).  Same Woop arithmetic on both sides: t is bit-identical.
+  (b) the reference's CPU tracer BVH::trace (oracle/_ref/ref_cpu, the reference's own sources, its OWN SplitBVHBuilder tree --
+      triangle ids do not depend on the tree) on C1's primaries, C2's primaries and diffuse rays and >= 1 Mi live rays of C5.
+      The three ref_cpu processes build their trees (single-threaded, 10-70 s) while the GPU part of the tests runs.
+      C4's 6.5 M-triangle tree would take the reference builder ~10 minutes: there the CPU side is the oracle's restatement
+      of BVH::trace (b2o_trace_mt, bit-exact against BVH::trace on the golden scenes) over the product-built arrays.
+"""
+import importlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import parity_util as P
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TMP = "/tmp/b2rt_parity"
+
+
+@pytest.fixture(scope="module")
+def wl():
+    return importlib.import_module("gpu-ray-tracing_b200.workloads")
+
+
+def _records(oracle, t):
+    return t.cpu().numpy().view(oracle.RESULT_DTYPE).reshape(-1)
+
+
+def _rays(oracle, t):
+    return t.cpu().numpy().view(oracle.RAY_DTYPE).reshape(-1)
+
+
+class RefCpuFarm:
+    """ref_cpu per scene, started early with --go-file: each builds its BVH, then waits for its rays file."""
+
+    def __init__(self, oracle):
+        sys.path.insert(0, ROOT)
+        import bench
+        self.oracle = oracle
+        self.jobs = {}
+        os.makedirs(TMP, exist_ok=True)
+        if not oracle.have_ref_cpu():
+            return
+        procs = max(1, len(os.sched_getaffinity(0)))
+        for name in ("c1", "c2", "c5"):
+            obj, sig, camera, c = bench._workload_obj(name, TMP)
+            base = os.path.join(TMP, "%s.%d" % (name, os.getpid()))
+            go, rays, res = base + ".go", base + ".rays", base + ".results"
+            for f in (go, rays, res):
+                if os.path.exists(f):
+                    os.remove(f)
+            p = subprocess.Popen([oracle.REF_CPU, "--obj", obj, "--rays-in", rays, "--results-out", res, "--procs", str(procs),
+                                  "--go-file", go], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+            self.jobs[name] = (p, go, rays, res)
+
+    def trace(self, name, rays):
+        """BVH::trace of `rays` (closest hit) on the scene of workload `name`."""
+        p, go, rays_path, res = self.jobs.pop(name)
+        self.oracle.write_rays(rays_path, rays)
+        open(go, "w").close()
+        out, err = p.communicate(timeout=1200)
+        assert p.returncode == 0, err[-500:]
+        got = self.oracle.read_results(res)
+        for f in (go, rays_path, res):
+            os.remove(f)
+        return got
+
+    def close(self):
+        for p, go, _, _ in self.jobs.values():
+            p.kill()
+
+
+@pytest.fixture(scope="module")
+def farm(oracle):
+    f = RefCpuFarm(oracle)
+    yield f
+    f.close()
+
+
+def _ref_gpu(oracle, cuda_bvh):
+    ref = oracle.RefGpuTracer()
+    ref.set_bvh(cuda_bvh.m_nodes, cuda_bvh.m_triWoop, cuda_bvh.m_triIndex)
+    return ref
+
+
+def _trace_ref_gpu(oracle, ref, rb, ctx):
+    out = torch.zeros_like(rb.m_results)
+    ref.trace(rb.getRayBuffer_dev(), out, not rb.getNeedClosestHit(), ctx.sm_count() * 32)
+    return _records(oracle, out[: rb.getSize()])
+
+
+def _trace_variant(oracle, ctx, tracer, rb, variant):
+    ctx.set_trace_config(variant=variant)
+    try:
+        tracer.traceBatch(rb)
+    finally:
+        ctx.set_trace_config()
+    return _records(oracle, rb.getResultBuffer_dev()).copy()
+
+
+def test_c1_primaries_against_bvh_trace(b2rt, oracle, ctx, wl, farm):
+    if "c1" not in farm.jobs:
+        pytest.skip("oracle/_ref/ref_cpu did not travel to this box")
+    scene, bvh = wl.build_scene_and_bvh("c1")
+    frame = wl.Frame("c1", scene, bvh.arrays(), "cuda:0", ctx)
+    rb = frame.batches[0][0]
+    assert rb.getSize() == 786432
+    frame.trace_all()
+    rays = _rays(oracle, rb.getRayBuffer_dev())
+    want = farm.trace("c1", rays)
+    for variant in (-1, 1, 108):
+        got = _trace_variant(oracle, ctx, frame.tracer, rb, variant)
+        print(P.check_closest(rays, got, want, scene.verts, scene.tris, "C1 primaries, variant %d vs BVH::trace" % variant,
+                              woop_vs_mt=True, other_tree=True))
+
+
+def test_c2_both_batches_against_both_reference_tracers(b2rt, oracle, ctx, wl, farm):
+    scene, bvh = wl.build_scene_and_bvh("c2")
+    frame = wl.Frame("c2", scene, bvh.arrays(), "cuda:0", ctx)
+    assert [rb.getSize() for rb, _ in frame.batches] == [786432, 786432]
+    frame.trace_all()
+    all_rays = np.concatenate([_rays(oracle, rb.getRayBuffer_dev()) for rb, _ in frame.batches])
+    cpu = farm.trace("c2", all_rays) if "c2" in farm.jobs else None
+    ref = _ref_gpu(oracle, frame.cuda_bvh) if oracle.have_ref_gpu() else None
+    lo = 0
+    for k, (rb, _) in enumerate(frame.batches):
+        n = rb.getSize()
+        rays = all_rays[lo:lo + n]
+        theirs = _trace_ref_gpu(oracle, ref, rb, ctx) if ref else None
+        for variant in (-1, 1, 108):
+            got = _trace_variant(oracle, ctx, frame.tracer, rb, variant)
+            if theirs is not None:
+                print(P.check_closest(rays, got, theirs, scene.verts, scene.tris, "C2 batch %d, variant %d vs reference kernel" % (k, variant), t_exact=True))
+            if cpu is not None:
+                print(P.check_closest(rays, got, cpu[lo:lo + n], scene.verts, scene.tris, "C2 batch %d, variant %d vs BVH::trace" % (k, variant),
+                                      woop_vs_mt=True, other_tree=True))
+        lo += n
+    assert ref is not None or cpu is not None, "neither reference tracer is on this box"
+
+
+def test_c5_batch_against_both_reference_tracers(b2rt, oracle, ctx, wl, farm):
+    scene, bvh = wl.build_scene_and_bvh("c5")
+    frame = wl.Frame("c5", scene, bvh.arrays(), "cuda:0", ctx)
+    rb = frame.batches[0][0]
+    n = rb.getSize()
+    assert n == 64 * 1024 * 1024
+    # (a) the whole batch, shipped default, against the reference kernel -- compared on the device, mismatches classified on the host
+    frame.trace_all()
+    if oracle.have_ref_gpu():
+        ref = _ref_gpu(oracle, frame.cuda_bvh)
+        out = torch.zeros_like(rb.m_results)
+        ref.trace(rb.getRayBuffer_dev(), out, False, ctx.sm_count() * 32)
+        mine = rb.getResultBuffer_dev()
+        same = mine[:, 0] == out[:n, 0]
+        agree = int(same.sum().item()) / n
+        assert agree >= P.ID_AGREE, "C5 whole batch: id agreement %.6f" % agree
+        hit = same & (mine[:, 0] >= 0)
+        assert bool((mine[:, 1][hit] == out[:n, 1][hit]).all()), "C5: t differs from the reference kernel's on equal ids"
+        bad = torch.nonzero(~same).flatten()
+        if bad.numel():
+            rays = _rays(oracle, rb.getRayBuffer_dev()[bad])
+            got, want = _records(oracle, mine[bad]), _records(oracle, out[:n][bad])
+            cls = P.classify_mismatches(rays, got, want, scene.verts, scene.tris, np.arange(len(rays)))
+            assert len(cls["unexplained"]) == 0, "C5: %d of %d id mismatches unexplained" % (len(cls["unexplained"]), len(rays))
+            print("C5 whole batch vs reference kernel: agreement %.7f, %d mismatches: %s" % (
+                agree, len(rays), {k: v for k, v in cls.items() if k != "unexplained"}))
+        # the binary kernel on an 8 Mi-ray slice from the middle of the batch
+        lo = 28 * 1024 * 1024
+        sl = wl._slice_buffer(rb, lo, lo + 8 * 1024 * 1024, closest=True)
+        got = _trace_variant(oracle, ctx, frame.tracer, sl, 1)
+        want = _records(oracle, out[lo:lo + 8 * 1024 * 1024])
+        print(P.check_closest(_rays(oracle, sl.getRayBuffer_dev()), got, want, scene.verts, scene.tris,
+                              "C5 8 Mi-ray slice, variant 1 vs reference kernel", t_exact=True))
+        del out, sl
+    # (b) >= 1 Mi live rays, evenly spread over the batch, against BVH::trace
+    if "c5" in farm.jobs:
+        live = torch.nonzero(rb.getRayBuffer_dev()[:, 7] >= rb.getRayBuffer_dev()[:, 3]).flatten()
+        pick = live[:: max(1, live.numel() // (1 << 20))][: (1 << 20) + 4096]
+        assert pick.numel() >= 1 << 20
+        sub = wl._gather_buffer(rb, pick)
+        sub.setNeedClosestHit(True)
+        rays = _rays(oracle, sub.getRayBuffer_dev())
+        want = farm.trace("c5", rays)
+        for variant in (-1, 1):
+            got = _trace_variant(oracle, ctx, frame.tracer, sub, variant)
+            print(P.check_closest(rays, got, want, scene.verts, scene.tris, "C5 %d live rays, variant %d vs BVH::trace" % (len(rays), variant),
+                                  woop_vs_mt=True, other_tree=True))
+
+
+def _trace_mt_parallel(oracle, arrays, scene, rays, procs):
+    """b2o_trace_mt (the restatement of BVH::trace) over forked workers."""
+    import multiprocessing as mp
+    global _MT_STATE
+    _MT_STATE = (oracle, {k: np.ascontiguousarray(v) for k, v in arrays.items() if k != "layout"},
+                 {"verts": scene.verts, "tris": scene.tris}, rays)
+    bounds = [(len(rays) * p // procs, len(rays) * (p + 1) // procs) for p in range(procs)]
+    with mp.get_context("fork").Pool(procs) as pool:
+        parts = pool.map(_mt_worker, bounds)
+    return np.concatenate(parts)
+
+
+_MT_STATE = None
+
+
+def _mt_worker(b):
+    oracle, arrays, sc, rays = _MT_STATE
+    return oracle.trace_mt(arrays, sc, rays[b[0]:b[1]])
+
+
+def test_c4_against_reference_kernel_and_bvh_trace_restatement(b2rt, oracle, ctx, wl):
+    scene, bvh = wl.build_scene_and_bvh("c4")
+    arrays = bvh.arrays()
+    frame = wl.Frame("c4", scene, arrays, "cuda:0", ctx)
+    batches = [frame.primary] + [rb for rb, _ in frame.batches]
+    assert [rb.getSize() for rb in batches] == [786432, 786432]
+    ref = _ref_gpu(oracle, frame.cuda_bvh) if oracle.have_ref_gpu() else None
+    procs = max(1, len(os.sched_getaffinity(0)))
+    for k, rb in enumerate(batches):
+        rays = _rays(oracle, rb.getRayBuffer_dev())
+        theirs = _trace_ref_gpu(oracle, ref, rb, ctx) if ref else None
+        live = rays["tmax"] >= rays["tmin"]
+        sel = np.nonzero(live)[0][:: 3 if k else 1]                # every ray of the primary batch, a third of the live diffuse rays
+        cpu_sel = _trace_mt_parallel(oracle, arrays, scene, rays[sel], procs)
+        for variant in (-1, 1):
+            got = _trace_variant(oracle, ctx, frame.tracer, rb, variant)
+            if theirs is not None:
+                print(P.check_closest(rays, got, theirs, scene.verts, scene.tris, "C4 batch %d, variant %d vs reference kernel" % (k, variant), t_exact=True))
+            print(P.check_closest(rays[sel], got[sel], cpu_sel, scene.verts, scene.tris,
+                                  "C4 batch %d, variant %d vs BVH::trace restatement" % (k, variant), woop_vs_mt=True))
