@@ -12,6 +12,7 @@ LAYOUT_COMPACT2 = 5
 TRACE_ANY_HIT = 1
 TRACE_WRITE_BARY = 2
 TRACE_STATS = 4
+COUNT_HITS_STATIC_MAX = 16 * 1024 * 1024
 TUNE_NO_STREAM, TUNE_GREEDY_WIDE, TUNE_L2_WINDOW = 1, 4, 8
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmin", "<f4"), ("d", "<f4", 3), ("tmax", "<f4")])
@@ -76,6 +77,7 @@ _SIGNATURES = {
     "b2rt_morton_keys": (i32, [vp, vp, i64, vp, vp, vp]),
     "b2rt_reorder_rays": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, vp]),
     "b2rt_count_hits": (i32, [vp, vp, i64, C.POINTER(i64), vp]),
+    "b2rt_count_hits_static": (i32, [vp, i64, vp, vp]),
     "b2rt_reconstruct": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]),
     "b2rt_pixel_table": (i32, [i32, i32, vp, vp]),
     "b2rt_camera_matrices": (i32, [vp, vp, vp, f32, f32, f32, i32, i32, vp, vp]),

@@ -33,6 +33,7 @@ CUDA_SOURCES = [
     ("raysort.cu", ["-fmad=false"]),
     ("misc.cu", ["-fmad=false"]),
     ("woopify.cu", ["-fmad=false"]),
+    ("static_scratch.cu", []),
 ]
 HOST_SOURCES = ["host/bvh_builder.cpp", "host/host_util.cpp", "host/wide_bvh.cpp"]
 HOST_FLAGS = ["-O2", "-ffp-contract=off", "-fPIC", "-std=c++17", "-pthread", "-Wall", "-I", INCLUDE]

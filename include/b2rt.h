@@ -164,6 +164,16 @@ int b2rt_reorder_rays(b2rt_ctx* ctx, const void* keys_dev, const void* in_rays_d
  * number of results with id >= 0.  Synchronous. */
 int b2rt_count_hits(b2rt_ctx* ctx, const void* results_dev, int64_t num_rays, int64_t* hits,
                     void* stream);
+/* NO counterpart in the reference: added for callers that cannot allocate (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The hit count of b2rt_count_hits
+ * without a context and without any allocation: scratch lives in a file-scope device array of the library (33 KB, held by
+ * every GPU that loads the library until the process exits), the total is written to the DEVICE word hits_dev, and the
+ * call only enqueues an 8-byte memset and one kernel on `stream` (current device; asynchronous, no synchronisation, no
+ * cudaMalloc / cudaFree).  num_rays above B2RT_COUNT_HITS_STATIC_MAX is refused with B2RT_ERR_ARG; errors of this
+ * context-less call are read with b2rt_last_error(NULL).  All calls on a device share the scratch: calls that overlap on
+ * the GPU (different streams) race; calls on one stream are safe.  csrc/static_scratch.cu. */
+#define B2RT_COUNT_HITS_STATIC_MAX (16 * 1024 * 1024)
+int b2rt_count_hits_static(const void* results_dev, int64_t num_rays, int64_t* hits_dev, void* stream);
 /* replaces launch_reconstructKernel (RendererKernels.hh:54-70, RendererKernels.cu:60-108):
  * ABGR pixel from the batch's hit ids.  mode: 0 primary, 1 AO, 2 diffuse. */
 int b2rt_reconstruct(b2rt_ctx* ctx, int num_rays_per_primary, int first_primary, int num_primary,
