@@ -12,6 +12,7 @@ LAYOUT_COMPACT2 = 5
 TRACE_ANY_HIT = 1
 TRACE_WRITE_BARY = 2
 TRACE_STATS = 4
+TRACE_WATERTIGHT = 8
 COUNT_HITS_STATIC_MAX = 16 * 1024 * 1024
 TUNE_NO_STREAM, TUNE_GREEDY_WIDE, TUNE_L2_WINDOW = 1, 4, 8
 

@@ -359,7 +359,7 @@ int b2rt_trace_host_begin(b2rt_ctx* ctx, const void* raysHost, void* resultsHost
     char* dRes = dRays + rayBytes;
     const char* hRays = static_cast<const char*>(raysHost);
     char* hRes = static_cast<char*>(resultsHost);
-    const bool clearPads = !(flags & (B2RT_TRACE_WRITE_BARY | B2RT_TRACE_STATS));
+    const bool clearPads = !(flags & (B2RT_TRACE_WRITE_BARY | B2RT_TRACE_STATS | B2RT_TRACE_WATERTIGHT));
     cudaError_t e = cudaEventRecord(slot.evT0, ctx->sIn);
     for (int c = 0; c < chunks && e == cudaSuccess && rc == 0; c++) {
         const int64_t lo = c * per, n = std::min<int64_t>(per, numRays - lo);

@@ -181,6 +181,47 @@ __device__ __forceinline__ float faddFtz(float a, float b)
 __device__ __forceinline__ float woopDot(float dx, float dy, float dz, const float4 r) { return ffmaFtz(dz, r.z, ffmaFtz(dx, r.x, fmulFtz(dy, r.y))); }
 __device__ __forceinline__ float woopPlane(float ox, float oy, float oz, const float4 r) { return ffmaFtz(oz, r.z, ffmaFtz(oy, r.y, ffmaFtz(ox, r.x, r.w))); }
 
+// B2RT_TRACE_WATERTIGHT: the acceptance test of a triangle with an edge tolerance (the reference's is exact, u >= 0, v >= 0,
+// u + v <= 1, kepler_dynamic_fetch.cu:349-364: a ray aimed at the edge two triangles share can fail both by one rounding and
+// leak through a closed surface -- 2.8 % of the rays aimed at the diagonal of a split quad do, tests/test_gpu_watertight.py).
+// u = r . P + w with P = o + t d the hit point and (r, w) a row of the float32 inverse CudaBVH.cc:361-380 stores: |r| is one
+// over the triangle's edge length, so the row's rounding alone moves u by ulp x |r| |P| -- far more than an ulp of u's own
+// terms, which nearly cancel (measured: v = -1.1e-6 from the stored rows for a point 5e-7 INSIDE the triangle).  The
+// tolerance is therefore scaled by the row magnitudes:  eps_u = 4 ulp x (|r.x| |P.x| + |r.y| |P.y| + |r.z| |P.z| + |w|),  with
+// |P.k| bounded by |o.k| + |t d.k| -- a position error of a few ulps of the coordinates, expressed in barycentric units.
+// With it a ray on a shared edge hits BOTH triangles; which one is reported must then not depend on the order the traversal
+// meets them in (that is: on the ray's warp-mates), so of two hits at exactly the same t the one with the lower triangle id
+// wins, and boxes are culled against hitT widened by 2^-20 so that the other candidate of an exact tie is always still
+// visited.  Results of a batch are then identical under any permutation of its rays.
+constexpr float kWatertightEps = 4.0f / 16777216.0f;        // 4 ulps
+struct WtRay { float ox, oy, oz, dx, dy, dz; };
+template <bool WT>
+__device__ __forceinline__ bool woopAccept(float t, float tmin, float hitT, float u, float v, const float4 r1, const float4 r2,
+                                           const WtRay& q, int row, int hitRow, const int* __restrict__ triIndex)
+{
+    if (!WT) return t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && faddFtz(u, v) <= 1.0f;
+    const float hx = __fmaf_rn(fabsf(t), fabsf(q.dx), fabsf(q.ox)), hy = __fmaf_rn(fabsf(t), fabsf(q.dy), fabsf(q.oy)),
+                hz = __fmaf_rn(fabsf(t), fabsf(q.dz), fabsf(q.oz));
+    const float eu = kWatertightEps * __fmaf_rn(fabsf(r1.x), hx, __fmaf_rn(fabsf(r1.y), hy, __fmaf_rn(fabsf(r1.z), hz, fabsf(r1.w))));
+    const float ev = kWatertightEps * __fmaf_rn(fabsf(r2.x), hx, __fmaf_rn(fabsf(r2.y), hy, __fmaf_rn(fabsf(r2.z), hz, fabsf(r2.w))));
+    if (!(t > tmin && t <= hitT && u >= -eu && v >= -ev && u + v <= 1.0f + eu + ev)) return false;
+    if (t < hitT) return true;
+    return hitRow >= 0 && __ldg(triIndex + row) < __ldg(triIndex + hitRow);           // exact tie: the lower triangle id
+}
+__device__ __forceinline__ float watertightCull(float hitT) { return hitT * (1.0f + 1.0f / 1048576.0f); }
+// ... and the BOX test has to be conservative too: shared vertices and edges are the extreme points of leaf boxes, and the slab
+// distances fma(plane, idir, -orig * idir) (kepler_dynamic_fetch.cu:227-246) carry an ABSOLUTE error of an ulp of |orig * idir|
+// (the product is rounded before the subtraction cancels it) plus the relative error of rcp.approx.  Watertight kernels accept
+// a box when  tmax (1 + 2^-21) + slack >= tmin  with slack = 2^-21 max_axis |orig * idir|, computed once per ray.
+__device__ __forceinline__ float watertightSlack(float oodx, float oody, float oodz)
+{
+    return (1.0f / 2097152.0f) * fmaxf(fmaxf(fabsf(oodx), fabsf(oody)), fabsf(oodz));
+}
+__device__ __forceinline__ bool watertightOverlap(float cmin, float cmax, float slack)
+{
+    return __fmaf_rn(cmax, 1.0f + 1.0f / 2097152.0f, slack) >= cmin;
+}
+
 // shared-memory loads through a 32-bit shared-window address (read-only data staged before a barrier)
 __device__ __forceinline__ float4 lds128(unsigned addr)
 {

@@ -67,7 +67,7 @@ constexpr int kShareRounds = 4;     // stack entries a lane may hand over per vi
 constexpr int kShareQueue = 128;    // queue entries (int4: ray, stack entry, hit distance); 2 KB keeps the L1 carve-out where it was
 constexpr int kShareList = 1024;    // shared rays per CTA (global memory, one slice per CTA and launch slot)
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF, bool WT>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TraceParams p)
 {
     extern __shared__ float4 s_dyn[];
@@ -109,6 +109,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
     float origx = 0, origy = 0, origz = 0, dirx = 0, diry = 0, dirz = 0;
     float idirx = 0, idiry = 0, idirz = 0, oodx = 0, oody = 0, oodz = 0, tmin = 0, hitT = 0;
     float hitU = 0, hitV = 0;
+    float cullT = 0, slack = 0;         // WT: hitT widened for the box tests, absolute slack of the slab distances (common.cuh)
     int hitIndex = -1, rayidx = -1;
     int nodeAddr = kSentinel;           // >= 0 inner node, < 0 leaf, sentinel = finished
     int leafAddr = 0;                   // postponed leaf (< 0) or none (>= 0)
@@ -188,11 +189,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     else { o = ldg4(p.rays + 2 * (size_t)idx); d = ldg4(p.rays + 2 * (size_t)idx + 1); }
                     origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
                     dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
+                    if (WT) cullT = hitT;
                     const float ooeps = 8.271806125530277e-25f;    // 2^-80, avoids division by zero
                     idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
                     idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
                     idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
                     oodx = origx * idirx; oody = origy * idiry; oodz = origz * idirz;
+                    if (WT) slack = watertightSlack(oodx, oody, oodz);
                     // stack: memory slot 0 and the register both hold the sentinel
                     stackStore(0, kSentinel);
                     sp = 1; tos = kSentinel;
@@ -284,11 +287,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                             const float4 d = ldg4(p.rays + 2 * (size_t)rayidx + 1);
                             origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
                             dirx = d.x; diry = d.y; dirz = d.z; hitT = __int_as_float(item.z);
+                            if (WT) cullT = hitT;
                             const float ooeps = 8.271806125530277e-25f;
                             idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
                             idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
                             idirz = rcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
                             oodx = origx * idirx; oody = origy * idiry; oodz = origz * idirz;
+                            if (WT) slack = watertightSlack(oodx, oody, oodz);
                             hitIndex = -1; viaAtomic = true; giveSlot = 2;
                             stackStore(0, kSentinel);
                             sp = 1; tos = kSentinel;
@@ -345,12 +350,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                 const float c1lox = __fmaf_rn(n1xy.x, idirx, -oodx), c1hix = __fmaf_rn(n1xy.y, idirx, -oodx);
                 const float c1loy = __fmaf_rn(n1xy.z, idiry, -oody), c1hiy = __fmaf_rn(n1xy.w, idiry, -oody);
                 const float c0min = fmax3(fminf(c0lox, c0hix), fminf(c0loy, c0hiy), fmaxf(fminf(c0loz, c0hiz), tmin));
-                const float c0max = fmin3(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy), fminf(fmaxf(c0loz, c0hiz), hitT));
+                const float c0max = fmin3(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy), fminf(fmaxf(c0loz, c0hiz), WT ? cullT : hitT));
                 const float c1min = fmax3(fminf(c1lox, c1hix), fminf(c1loy, c1hiy), fmaxf(fminf(c1loz, c1hiz), tmin));
-                const float c1max = fmin3(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy), fminf(fmaxf(c1loz, c1hiz), hitT));
+                const float c1max = fmin3(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy), fminf(fmaxf(c1loz, c1hiz), WT ? cullT : hitT));
 
-                const bool trav0 = (c0max >= c0min);
-                const bool trav1 = (c1max >= c1min);
+                const bool trav0 = WT ? watertightOverlap(c0min, c0max, slack) : (c0max >= c0min);
+                const bool trav1 = WT ? watertightOverlap(c1min, c1max, slack) : (c1max >= c1min);
                 if (!trav0 && !trav1) {
                     nodeAddr = pop();
                 } else {
@@ -397,8 +402,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                         const float Oy = woopPlane(origx, origy, origz, v22);
                         const float Dy = woopDot(dirx, diry, dirz, v22);
                         const float v = ffmaFtz(t, Dy, Oy);
-                        if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && faddFtz(u, v) <= 1.0f) {
+                        if (woopAccept<WT>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, triAddr, hitIndex, p.triIndex)) {
                             hitT = t; hitIndex = triAddr;
+                            if (WT) cullT = watertightCull(t);
                             if (BARY) { hitU = u; hitV = v; }
                             if (ANY_HIT) { nodeAddr = kSentinel; break; }
                         }
@@ -413,6 +419,16 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                         const float Oz = woopPlane(-origx, -origy, -origz, v00);
                         const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
                         const float t = fmulFtz(Oz, invDz);
+                        if (WT) {
+                            const float Ox = woopPlane(origx, origy, origz, v11), Dx = woopDot(dirx, diry, dirz, v11);
+                            const float Oy = woopPlane(origx, origy, origz, v22), Dy = woopDot(dirx, diry, dirz, v22);
+                            const float u = ffmaFtz(t, Dx, Ox), v = ffmaFtz(t, Dy, Oy);
+                            if (woopAccept<true>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, triAddr, hitIndex, p.triIndex)) {
+                                hitT = t; hitIndex = triAddr; cullT = watertightCull(t);
+                                if (BARY) { hitU = u; hitV = v; }
+                                if (ANY_HIT) { nodeAddr = kSentinel; break; }
+                            }
+                        } else
                         if (t > tmin && t < hitT) {
                             const float Ox = woopPlane(origx, origy, origz, v11);
                             const float Dx = woopDot(dirx, diry, dirz, v11);
@@ -504,10 +520,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 // ---------------------------------------------------------------------------------------------
 struct Variant { int block; int stackSmem; int minBlocks; };
 
-template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF>
+template <bool ANY_HIT, bool BARY, bool STATS, int STACK_SMEM, int BLOCK, int MIN_BLOCKS, int LEAF, bool WT = false>
 static int launchOne(b2rt_ctx* ctx, TraceParams& p, cudaStream_t stream)
 {
-    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>;
+    auto kern = traceKernel<ANY_HIT, BARY, STATS, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF, WT>;
     // any-hit kernels carry the sharing queue behind the staged nodes; the small-CTA default gives up 40 nodes for it so
     // that four CTAs still fit the 164 KB shared-memory step (the next step, 196 KB, costs 32 KB of L1)
     constexpr size_t shareBytes = ANY_HIT ? sizeof(ShareArea) + (size_t)kShareQueue * sizeof(int4) : 0;
@@ -549,6 +565,9 @@ static int launchFlags(b2rt_ctx* ctx, TraceParams& p, unsigned flags, cudaStream
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
+    if (flags & B2RT_TRACE_WATERTIGHT)          // always writes barycentrics, never instrumented (two kernels per shape instead of six)
+        return any ? launchOne<true, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF, true>(ctx, p, stream)
+                   : launchOne<false, true, false, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF, true>(ctx, p, stream);
     if (flags & B2RT_TRACE_STATS) {
         // the instrumented build always writes barycentrics (one kernel fewer to carry)
         return any ? launchOne<true, true, true, STACK_SMEM, BLOCK, MIN_BLOCKS, LEAF>(ctx, p, stream)

@@ -70,7 +70,7 @@ __device__ __forceinline__ void storeResultT(const WideParams& p, unsigned rayid
 // are the refill's atomic -> ray-load chain -- but a chunk is 16 samples of ONE primary ray, so 52 % of the C5 chunks are
 // entirely degenerate and a refill often fills no lane: 20 % more instructions, 40 % instead of 50 % of the warp slots
 // occupied, 3 265 -> 2 380 Mrays/s.
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, bool WT>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
     auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
@@ -93,6 +93,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 
     float origx = 0, origy = 0, origz = 0, dirx = 0, diry = 0, dirz = 0;
     float idirx = 0, idiry = 0, idirz = 0, tmin = 0, hitT = 0, hitU = 0, hitV = 0;
+    float cullT = 0;                    // WT: hitT widened for the box tests (common.cuh:woopAccept)
     int hitIndex = -1, rayidx = -1, sp = 0;
     unsigned octinv4 = 0;
     uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
@@ -106,6 +107,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         rayidx = (int)idx;
         origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
         dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;
+        if (WT) cullT = hitT;
         const float ooeps = 8.271806125530277e-25f;    // 2^-80 (kepler_dynamic_fetch.cu:134-137)
         idirx = rcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
         idiry = rcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
@@ -178,6 +180,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 const float bz = __fmaf_rn(q0.z - origz, idirz, -az);
                 // entry / exit planes by ray direction: no per-child min/max over the two planes of an axis
                 const bool nx = idirx < 0.0f, ny = idiry < 0.0f, nz = idirz < 0.0f;     // idir is never zero (2^-80 clamp keeps the sign)
+                // WT: the decoded planes t = (1 + q 2^-15) ax + b carry an error of an ulp of |b| (~2^15 cells: 2^-9 of a cell), which the
+                // 1/64-cell margin of the quantised boxes covers for ordinary nodes; a node far from the ray's origin relative to its
+                // size (|b| >> 2^15 cells is impossible: b is measured from the node's own origin) needs no more.  The slack below
+                // covers rcp.approx and the last rounding.
+                const float wslack = WT ? (1.0f / 2097152.0f) * fmaxf(fmaxf(fabsf(bx), fabsf(by)), fabsf(bz)) : 0.0f;
                 unsigned hitmask = 0;
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
@@ -203,8 +210,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                         const float t1y = __fmaf_rn(byteToUnitFloat<J>(farY, one) , ay, by);                            \
                         const float t1z = __fmaf_rn(byteToUnitFloat<J>(farZ, one) , az, bz);                            \
                         const float cmin = fmax3(t0x, t0y, fmaxf(t0z, tmin));                                      \
-                        const float cmax = fmin3(t1x, t1y, fminf(t1z, hitT));                                      \
-                        if (cmin <= cmax) hitmask |= ((childBits4 >> (8 * J)) & 0xFFu) << ((bitIndex4 >> (8 * J)) & 0xFFu); \
+                        const float cmax = fmin3(t1x, t1y, fminf(t1z, WT ? cullT : hitT));                                      \
+                        if (WT ? watertightOverlap(cmin, cmax, wslack) : (cmin <= cmax)) hitmask |= ((childBits4 >> (8 * J)) & 0xFFu) << ((bitIndex4 >> (8 * J)) & 0xFFu); \
                     }
                     B2RT_WIDE_CHILD(0) B2RT_WIDE_CHILD(1) B2RT_WIDE_CHILD(2) B2RT_WIDE_CHILD(3)
 #undef B2RT_WIDE_CHILD
@@ -246,8 +253,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                     const float Oy = woopPlane(origx, origy, origz, v22);
                     const float Dy = woopDot(dirx, diry, dirz, v22);
                     const float v = ffmaFtz(t, Dy, Oy);
-                    if (t > tmin && t < hitT && u >= 0.0f && v >= 0.0f && faddFtz(u, v) <= 1.0f) {
+                    if (woopAccept<WT>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, tri, hitIndex, p.triIndex)) {
                         hitT = t; hitIndex = tri;
+                        if (WT) cullT = watertightCull(t);
                         if (BARY) { hitU = u; hitV = v; }
                         if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; }
                     }
@@ -269,6 +277,16 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 const float Oz = woopPlane(-origx, -origy, -origz, v00);
                 const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
                 const float t = fmulFtz(Oz, invDz);
+                if (WT) {
+                    const float Ox = woopPlane(origx, origy, origz, v11), Dx = woopDot(dirx, diry, dirz, v11);
+                    const float Oy = woopPlane(origx, origy, origz, v22), Dy = woopDot(dirx, diry, dirz, v22);
+                    const float u = ffmaFtz(t, Dx, Ox), v = ffmaFtz(t, Dy, Oy);
+                    if (woopAccept<true>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, tri, hitIndex, p.triIndex)) {
+                        hitT = t; hitIndex = tri; cullT = watertightCull(t);
+                        if (BARY) { hitU = u; hitV = v; }
+                        if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; }
+                    }
+                } else
                 if (t > tmin && t < hitT) {
                     const float Ox = woopPlane(origx, origy, origz, v11);
                     const float Dx = woopDot(dirx, diry, dirz, v11);
@@ -314,10 +332,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, bool WT = false>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, WT>;
     int blocksPerSm = 0;
     const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2);
     { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
@@ -356,6 +374,9 @@ static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStr
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
+    if (flags & B2RT_TRACE_WATERTIGHT)
+        return any ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, true>(ctx, p, stream)
+                   : launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, true>(ctx, p, stream);
     if (flags & B2RT_TRACE_STATS)
         return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
                    : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);

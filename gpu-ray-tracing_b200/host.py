@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 from ._lib import (BuildParams, B2rtError, LAYOUT_COMPACT2, RAY_DTYPE, RESULT_DTYPE, TRACE_ANY_HIT,
-                   TRACE_STATS, TRACE_WRITE_BARY, TraceConfig, TraceStats, check, lib, np_ptr, scenes_lib)
+                   TRACE_STATS, TRACE_WATERTIGHT, TRACE_WRITE_BARY, TraceConfig, TraceStats, check, lib, np_ptr, scenes_lib)
 
 SCENE_KINDS = {"blob": 0, "interior": 1, "knot": 2, "strands": 3}
 
@@ -467,6 +467,7 @@ class CudaTracer:
         self.m_kernelConfig = None
         self.writeBarycentrics = False
         self.collectStats = False
+        self.watertight = False         # B2RT_TRACE_WATERTIGHT: edge-tolerant Woop test, order-independent closest hit
         self.initKernel()
 
     def initKernel(self):
@@ -510,6 +511,8 @@ class CudaTracer:
             flags |= TRACE_WRITE_BARY
         if self.collectStats:
             flags |= TRACE_STATS
+        if self.watertight:
+            flags |= TRACE_WATERTIGHT
         ms = C.c_float()
         check(lib().b2rt_trace(self._ctx.handle, _dptr(rays.m_rays), _dptr(rays.m_results), numRays, flags,
                                _stream_ptr(), C.byref(ms)), self._ctx.handle)
@@ -519,6 +522,8 @@ class CudaTracer:
         flags = 0 if rays.getNeedClosestHit() else TRACE_ANY_HIT
         if self.writeBarycentrics:
             flags |= TRACE_WRITE_BARY
+        if self.watertight:
+            flags |= TRACE_WATERTIGHT
         if rays.getSize():
             check(lib().b2rt_trace(self._ctx.handle, _dptr(rays.m_rays), _dptr(rays.m_results), rays.getSize(), flags,
                                    _stream_ptr(), None), self._ctx.handle)

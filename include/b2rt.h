@@ -56,6 +56,9 @@ typedef enum {
 /* b2rt_trace flags */
 #define B2RT_TRACE_ANY_HIT     1u  /* !RayBuffer::getNeedClosestHit()              CudaTracer.cc:172 */
 #define B2RT_TRACE_WRITE_BARY  2u  /* store u,v in RayResult.padA/padB             (superset) */
+#define B2RT_TRACE_WATERTIGHT  8u  /* edge-tolerant Woop test + order-independent closest hit: no leaks through shared edges, the same
+                                      record for a ray wherever it sits in the batch.  Off by default: the reference's test is exact
+                                      (kepler_dynamic_fetch.cu:349-364) and so is parity with it.  Implies WRITE_BARY. */
 #define B2RT_TRACE_STATS       4u  /* instrumented kernel: fills b2rt_trace_stats (include/b2rt_tools.h; slower) */
 
 /* Tunables of the traversal kernel; zero-initialise and override what you need. */
