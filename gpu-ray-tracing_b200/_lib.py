@@ -95,6 +95,25 @@ _SIGNATURES = {
     "b2rt_wide_arrays": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz), vp]),
 }
 
+class MgStats(C.Structure):
+    _fields_ = [("rays", C.c_int64), ("hits", C.c_int64), ("ms_trace_max", C.c_float), ("ms_trace_min", C.c_float),
+                ("ms_with_gather_max", C.c_float), ("ms_per_device", C.c_float * 16)]
+
+
+# include/b2rt_mg.h (same library)
+_MG_SIGNATURES = {
+    "b2rt_mg_create": (i32, [i32, vp, C.POINTER(vp)]),
+    "b2rt_mg_destroy": (None, [vp]),
+    "b2rt_mg_last_error": (C.c_char_p, [vp]),
+    "b2rt_mg_num_devices": (i32, [vp]),
+    "b2rt_mg_context": (vp, [vp, i32]),
+    "b2rt_mg_stream": (vp, [vp, i32]),
+    "b2rt_mg_broadcast_bvh": (i32, [vp, vp, sz, vp, sz, vp, sz, i32, i32]),
+    "b2rt_mg_trace": (i32, [vp, vp, vp, vp, C.c_uint, vp, C.POINTER(MgStats)]),
+    "b2rt_mg_trace_host": (i32, [vp, vp, vp, i64, C.c_uint, C.POINTER(MgStats)]),
+}
+MG_EXPORTS = sorted(_MG_SIGNATURES)
+
 _SCENE_SIGNATURES = {
     "b2rt_scene_generate": (i32, [i32, i32, C.c_uint64, C.POINTER(vp)]),
     "b2rt_scene_free": (None, [vp]),
@@ -106,6 +125,7 @@ _SCENE_SIGNATURES = {
 # what include/b2rt.h declares, what include/b2rt_tools.h adds (instrumentation), what libb2rt_scenes.so exports
 TOOLS_EXPORTS = sorted(["b2rt_get_trace_stats", "b2rt_count_work", "b2rt_wide_build", "b2rt_wide_free", "b2rt_wide_arrays"])
 EXPORTS = sorted(n for n in _SIGNATURES if n not in TOOLS_EXPORTS)
+_SIGNATURES.update(_MG_SIGNATURES)
 SCENES_EXPORTS = sorted(_SCENE_SIGNATURES)
 SCENES_LIB_PATH = os.path.join(HERE, "libb2rt_scenes.so")
 _scenes = None

@@ -34,6 +34,7 @@ CUDA_SOURCES = [
     ("misc.cu", ["-fmad=false"]),
     ("woopify.cu", ["-fmad=false"]),
     ("static_scratch.cu", []),
+    ("multi_gpu.cu", []),
 ]
 HOST_SOURCES = ["host/bvh_builder.cpp", "host/host_util.cpp", "host/wide_bvh.cpp"]
 HOST_FLAGS = ["-O2", "-ffp-contract=off", "-fPIC", "-std=c++17", "-pthread", "-Wall", "-I", INCLUDE]
@@ -59,7 +60,7 @@ def _run(cmd, verbose):
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "wide_bvh.h"), os.path.join(INCLUDE, "b2rt.h"),
-               os.path.join(INCLUDE, "b2rt_tools.h"), os.path.abspath(__file__)]
+               os.path.join(INCLUDE, "b2rt_tools.h"), os.path.join(INCLUDE, "b2rt_mg.h"), os.path.abspath(__file__)]
     objs = []
     log = []
     for src, extra in CUDA_SOURCES:
@@ -75,7 +76,7 @@ def build(force=False, verbose=False):
         if force or not _newer(o, [s] + headers):
             log.append(_run([CXX] + HOST_FLAGS + ["-c", s, "-o", o], verbose))
     if force or not _newer(LIB, objs):
-        log.append(_run([NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lpthread"], verbose))
+        log.append(_run([NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lpthread", "-ldl"], verbose))
     scenes_src = os.path.join(CSRC, "host", "scenegen.cpp")
     if force or not _newer(SCENES_LIB, [scenes_src, os.path.join(INCLUDE, "b2rt_scenes.h"), os.path.abspath(__file__)]):
         log.append(_run([CXX] + HOST_FLAGS + ["-shared", scenes_src, "-o", SCENES_LIB], verbose))

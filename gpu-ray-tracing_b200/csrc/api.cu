@@ -90,7 +90,7 @@ static void relayoutNodes(const std::vector<float>& in, std::vector<float>& out,
     }
 }
 
-static void freeWide(b2rt_ctx* ctx)
+void freeWide(b2rt_ctx* ctx)
 {
     cudaFree(ctx->wideNodes);                   // one allocation: nodes, Woop rows, triangle ids
     ctx->wideNodes = nullptr; ctx->wideWoop = nullptr; ctx->wideTriIndex = nullptr;

@@ -135,6 +135,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
                     cudaStream_t stream);
+void freeWide(b2rt_ctx* ctx);
 int ensureWide(b2rt_ctx* ctx);      // builds the wide form from the private Compact2 copy if it is not there yet
 int uploadWide(b2rt_ctx* ctx, const void* nodes, size_t nodeBytes, const void* woop, size_t woopBytes, const void* tri,
                size_t triBytes, int numNodes, int numTris, int maxDepth, bool greedy, bool srcIsDevice);

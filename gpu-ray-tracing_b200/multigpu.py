@@ -145,3 +145,58 @@ def bind_to_local_cores(local_rank, local_world):
     except Exception as e:
         return {"bound": False, "why": str(e)}
     return {"bound": True, "cores": len(mine), "first": mine[0], "last": mine[-1], "gpu_local_cores": len(local)}
+
+
+class DeviceGroup:
+    """include/b2rt_mg.h from Python: ONE process driving several GPUs through the C ABI (b2rt_mg_create /
+    b2rt_mg_broadcast_bvh / b2rt_mg_trace / b2rt_mg_trace_host).  bench.py's N > 1 runs are one process per GPU under torchrun
+    (the driver's contract) and use the functions above; this class is what a C++ host holding all devices calls."""
+
+    def __init__(self, devices):
+        import ctypes as C
+        from ._lib import lib
+        self._C, self._lib = C, lib()
+        devs = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        rc = self._lib.b2rt_mg_create(len(devices), devs, C.byref(h))
+        if rc != 0:
+            raise RuntimeError("b2rt_mg_create: %s" % self._lib.b2rt_mg_last_error(None).decode())
+        self.handle, self.devices = h, list(devices)
+
+    def close(self):
+        if self.handle:
+            self._lib.b2rt_mg_destroy(self.handle)
+            self.handle = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError("b2rt_mg: %s" % self._lib.b2rt_mg_last_error(self.handle).decode())
+
+    def broadcast_bvh(self, arrays):
+        C = self._C
+        n = np.ascontiguousarray(arrays["nodes"], np.float32)
+        w = np.ascontiguousarray(arrays["woop"], np.float32)
+        t = np.ascontiguousarray(arrays["triIndex"], np.int32)
+        self._check(self._lib.b2rt_mg_broadcast_bvh(self.handle, n.ctypes.data_as(C.c_void_p), n.nbytes, w.ctypes.data_as(C.c_void_p), w.nbytes,
+                                                    t.ctypes.data_as(C.c_void_p), t.nbytes, int(arrays.get("layout", 5)), 0))
+
+    def trace(self, rays, results, gathered=None, any_hit=False):
+        """rays[r], results[r]: torch tensors on device r ([n_r, 8] float32, [n_r, 4] int32); gathered[r]: [sum n_r, 4] int32 or None."""
+        from ._lib import MgStats, TRACE_ANY_HIT
+        C = self._C
+        k = len(self.devices)
+        rp = (C.c_void_p * k)(*[r.data_ptr() if r.numel() else None for r in rays])
+        sp = (C.c_void_p * k)(*[r.data_ptr() if r.numel() else None for r in results])
+        cnt = (C.c_int64 * k)(*[int(r.shape[0]) for r in rays])
+        gp = (C.c_void_p * k)(*[g.data_ptr() for g in gathered]) if gathered is not None else None
+        st = MgStats()
+        self._check(self._lib.b2rt_mg_trace(self.handle, rp, sp, cnt, TRACE_ANY_HIT if any_hit else 0, gp, C.byref(st)))
+        return st
+
+    def trace_host(self, rays_host, results_host, any_hit=False):
+        from ._lib import MgStats, TRACE_ANY_HIT
+        C = self._C
+        st = MgStats()
+        self._check(self._lib.b2rt_mg_trace_host(self.handle, C.c_void_p(rays_host.ctypes.data), C.c_void_p(results_host.ctypes.data),
+                                                 len(rays_host), TRACE_ANY_HIT if any_hit else 0, C.byref(st)))
+        return st

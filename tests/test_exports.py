@@ -25,6 +25,9 @@ def test_header_symbols_exported(b2rt):
     # instrumentation entry points live in their own header (include/b2rt_tools.h), same library
     tools = [n for n in _declared("b2rt_tools.h") if n not in names]
     assert sorted(b2rt.TOOLS_EXPORTS) == tools and not [n for n in tools if not hasattr(lib, n)]
+    # the multi-GPU entry points (include/b2rt_mg.h) are in the same library; NCCL is bound at run time, so loading needs none
+    mg = [n for n in _declared("b2rt_mg.h") if n.startswith("b2rt_mg_")]
+    assert sorted(b2rt.MG_EXPORTS) == mg and not [n for n in mg if not hasattr(lib, n)]
     # the benchmark scenes are a separate host-only library (include/b2rt_scenes.h): nothing of it in libb2rt.so
     scenes = _declared("b2rt_scenes.h")
     sl = C.CDLL(b2rt.SCENES_LIB_PATH)
