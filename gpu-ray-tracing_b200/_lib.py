@@ -88,6 +88,8 @@ _SIGNATURES = {
     "b2rt_bvh_stats": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(f32), C.POINTER(i32)]),
     "b2rt_bvh_save": (i32, [vp, C.c_char_p]),
     "b2rt_bvh_load": (i32, [C.c_char_p, C.POINTER(vp)]),
+    "b2rt_bvhcache_key": (i32, [vp, i32, vp, i32, vp, f32, i32, i32, i32, C.POINTER(u32)]),
+    "b2rt_bvhcache_path": (i32, [C.c_char_p, u32, C.c_char_p, sz]),
     "b2rt_tri_normals": (i32, [vp, vp, i32, vp]),
     "b2rt_woopify": (i32, [vp, vp, vp, vp, vp, i64, vp, i64, vp]),
     "b2rt_wide_build": (i32, [vp, sz, vp, sz, vp, sz, C.POINTER(vp)]),

@@ -36,7 +36,7 @@ CUDA_SOURCES = [
     ("static_scratch.cu", []),
     ("multi_gpu.cu", []),
 ]
-HOST_SOURCES = ["host/bvh_builder.cpp", "host/host_util.cpp", "host/wide_bvh.cpp"]
+HOST_SOURCES = ["host/bvh_builder.cpp", "host/host_util.cpp", "host/wide_bvh.cpp", "host/bvhcache_key.cpp"]
 HOST_FLAGS = ["-O2", "-ffp-contract=off", "-fPIC", "-std=c++17", "-pthread", "-Wall", "-I", INCLUDE]
 
 

@@ -602,6 +602,7 @@ class Renderer:
         self.m_batchStart = 0
         self.m_cameraFar = 0.0
         self.m_buildParams = {"split_alpha": 1.0e-5}
+        self.m_bvhCachePath = None
 
     def setMesh(self, scene):
         if scene is self.m_scene:
@@ -619,9 +620,27 @@ class Renderer:
         self.m_bvh = CudaBVH(host_bvh, device=self.device)
 
     def getCudaBVH(self):
-        """Renderer::getCudaBVH (Renderer.cc:157-217) without the file cache."""
+        """Renderer::getCudaBVH (Renderer.cc:157-217): the BVH comes from <m_bvhCachePath>/%08x.dat when that file exists -- same
+        name and same bytes as a reference build's cache (b2rt_bvhcache_key) -- and is built and written there otherwise.
+        m_bvhCachePath = None (the default here; the reference uses "bvhcache") leaves the file system alone."""
         if self.m_bvh is None:
-            self.m_hostBVH = BVH(self.m_scene, split_alpha=self.m_buildParams["split_alpha"], min_leaf=1, max_leaf=8)
+            path = None
+            if self.m_bvhCachePath:
+                key = C.c_uint32()
+                check(lib().b2rt_bvhcache_key(np_ptr(self.m_scene.verts), len(self.m_scene.verts), np_ptr(self.m_scene.tris),
+                                              len(self.m_scene.tris), None, C.c_float(self.m_buildParams["split_alpha"]), 1, 8,
+                                              LAYOUT_COMPACT2, C.byref(key)))
+                buf = C.create_string_buffer(1024)
+                check(lib().b2rt_bvhcache_path(str(self.m_bvhCachePath).encode(), key.value, buf, 1024))
+                path = buf.value.decode()
+            import os
+            if path and os.path.exists(path):
+                self.m_hostBVH = BVH.load(path, self.m_scene)
+            else:
+                self.m_hostBVH = BVH(self.m_scene, split_alpha=self.m_buildParams["split_alpha"], min_leaf=1, max_leaf=8)
+                if path:
+                    os.makedirs(os.path.dirname(path), exist_ok=True)
+                    self.m_hostBVH.serialize(path)
             self.m_bvh = CudaBVH(self.m_hostBVH, device=self.device)
         return self.m_bvh
 

@@ -38,6 +38,19 @@ def describe(name):
         " x%d" % c["samples"] if c["ray_type"] != "primary" else "", ", Morton-sorted" if c["sort"] else "")
 
 
+def cache_path(scene, split_alpha=1.0e-5, min_leaf=1, max_leaf=8, cache_dir=None):
+    """File a reference build would use for this scene's CudaBVH: <dir>/%08x.dat with the key of Renderer::getCudaBVH
+    (b2rt_bvhcache_key: hashes of the scene's arrays, the platform, the build parameters and the layout)."""
+    import ctypes as C
+    from ._lib import LAYOUT_COMPACT2, check, lib, np_ptr
+    key = C.c_uint32()
+    check(lib().b2rt_bvhcache_key(np_ptr(scene.verts), len(scene.verts), np_ptr(scene.tris), len(scene.tris), None,
+                                  C.c_float(split_alpha), int(min_leaf), int(max_leaf), LAYOUT_COMPACT2, C.byref(key)))
+    buf = C.create_string_buffer(1024)
+    check(lib().b2rt_bvhcache_path((cache_dir or CACHE_DIR).encode(), key.value, buf, 1024))
+    return buf.value.decode()
+
+
 def describe_step(name):
     """What one bench step traces (identical text in both arms of bench.py)."""
     c = CONFIGS[name]
@@ -58,7 +71,7 @@ def build_scene_and_bvh(name, use_cache=True, log=None):
     t0 = time.time()
     scene = Scene.generate(c["kind"], c["tris"], c["seed"])
     t1 = time.time()
-    path = os.path.join(CACHE_DIR, "%s-%d-%d.dat" % (c["kind"], c["tris"], c["seed"]))
+    path = cache_path(scene)                # bvhcache/%08x.dat, the reference's naming (Renderer.cc:176-186)
     bvh = None
     if use_cache and os.path.exists(path):
         try:

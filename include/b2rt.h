@@ -214,6 +214,14 @@ int  b2rt_bvh_stats(const b2rt_host_bvh* bvh, int* inner_nodes, int* leaves, int
 /* bvhcache file format (Renderer.cc:176-211; CudaBVH.cc:79-97,113-116; Buffer.cc:327-361) */
 int  b2rt_bvh_save(const b2rt_host_bvh* bvh, const char* path);
 int  b2rt_bvh_load(const char* path, b2rt_host_bvh** out);
+/* The name Renderer::getCudaBVH gives the cache file of a BVH: <dir>/%08x.dat with
+ * key = hashBits(scene.hash(), platform.computeHash(), buildParams.computeHash(), layout)  (Renderer.cc:176-186; Scene.cc:94-102,
+ * bvh/Platform.hh:69, bvh/BVH.hh:82-85, framework/base/Hash.hh:181-196, Hash.cc:34-105), so that a bvhcache directory can be
+ * shared with a reference build.  verts / tris: the arrays of the reference's Scene for the mesh (vertices in the importer's
+ * order); tri_diffuse_rgba: 4 floats per triangle, or NULL for the default material (0.75 grey, 3d/Mesh.hh:92). */
+int  b2rt_bvhcache_key(const float* verts, int num_verts, const int32_t* tris, int num_tris, const float* tri_diffuse_rgba,
+                       float split_alpha, int min_leaf, int max_leaf, int layout, uint32_t* key);
+int  b2rt_bvhcache_path(const char* dir, uint32_t key, char* out, size_t cap);
 /* per-triangle normals as Scene does (rt/Scene.cc:72) */
 int  b2rt_tri_normals(const float* verts, const int32_t* tris, int num_tris, float* normals);
 /* The Woop rows of a Compact2 BVH computed on the device: replaces the per-triangle part of CudaBVH::createCompact /

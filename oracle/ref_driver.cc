@@ -149,7 +149,8 @@ static void usage(void)
         "        [--go-file F]                     after the BVH build, wait until file F exists before tracing\n"
         "        [--ao-out PREFIX --samples S --max-dist D [--sort]]   RayGen::ao batches from the primaries\n"
         "        [--trace-secondary [--secondary-closest] [--secondary-results-out F]]  time BVH::trace on the first secondary batch\n"
-        "        [--sort-in F --sort-out PREFIX]   RayBuffer::mortonSort\n");
+        "        [--sort-in F --sort-out PREFIX]   RayBuffer::mortonSort\n"
+        "        [--cache-key]                     the bvhcache file name key, computed by the reference's own hash code\n");
     exit(2);
 }
 
@@ -158,6 +159,7 @@ int main(int argc, char** argv)
     std::string obj, sceneOut, bvhOut, camSig, camOut, primOut, raysIn, resOut, aoOut, sortIn, sortOut;
     bool camAuto = false, anyHit = false, aoSort = false, secTrace = false, secClosest = false;
     std::string secResOut;
+    bool cacheKey = false;
     float alpha = 1.0e-5f, maxDist = 0.0f;
     int W = 1024, H = 768, procs = 1, samples = 1, limit = -1, repeat = 1;
     double budgetS = 0.0;
@@ -191,6 +193,7 @@ int main(int argc, char** argv)
         else if (a == "--trace-secondary") secTrace = true;       /* time BVH::trace on the first secondary batch */
         else if (a == "--secondary-closest") secClosest = true;   /* Diffuse: setNeedClosestHit(true), Renderer.cc:277 */
         else if (a == "--secondary-results-out") secResOut = next();
+        else if (a == "--cache-key") cacheKey = true;             /* print Renderer::getCudaBVH's cache file key (Renderer.cc:180-186) */
         else if (a == "--sort-in") sortIn = next();
         else if (a == "--sort-out") sortOut = next();
         else usage();
@@ -236,6 +239,13 @@ int main(int argc, char** argv)
             scene.getNumTriangles(), scene.getNumVertices(), stats.numInnerNodes, stats.numLeafNodes,
             stats.numTris, stats.SAHCost, buildSec);
 
+    if (cacheKey) {
+        /* exactly the expression of Renderer::getCudaBVH (Renderer.cc:180-186); the pieces: Scene.cc:94-102, Platform.hh:69, BVH.hh:82-85 */
+        U32 hs = scene.hash(), hp = platform.computeHash(), hb = params.computeHash();
+        fprintf(stdout, "{\"cache_key\": \"%08x\", \"scene_hash\": %u, \"platform_hash\": %u, \"params_hash\": %u, \"layout\": %d}\n",
+                hashBits(hs, hp, hb, (U32)BVHLayout_Compact2), hs, hp, hb, (int)BVHLayout_Compact2);
+        fflush(stdout);
+    }
     if (!sceneOut.empty()) {
         S32 hdr[3] = { 0x43533242 /* "B2SC" */, scene.getNumVertices(), scene.getNumTriangles() };
         FILE* f = fopen(sceneOut.c_str(), "wb"); if (!f) die("cannot write --scene-out");

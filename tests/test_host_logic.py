@@ -195,3 +195,39 @@ def test_leaf_references_cover_every_triangle_row(b2rt, kind, target):
     assert (woop[rows, 0] != 0x80000000).all()
     assert (tris == np.asarray(a["triIndex"])[rows]).all() and tris.min() >= 0 and tris.max() < len(scene.tris)
     assert len(rows) >= len(scene.tris)         # spatial splits only add references
+
+
+def test_bvhcache_key_and_reference_written_file(b2rt, tmp_path):
+    """Renderer::getCudaBVH names its cache file bvhcache/%08x.dat from hashes of the scene, the platform, the build parameters
+    and the layout (Renderer.cc:176-186).  tests/golden/cache_keys.json holds the keys the reference's own code computed for
+    the fixture scenes, tests/golden/bvhcache/<key>.dat a file the reference's CudaBVH::serialize wrote: the product computes
+    the same names, reads that file, and writes the same bytes back."""
+    import ctypes as C
+    import json
+    golden = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    keys = json.load(open(os.path.join(golden, "cache_keys.json")))
+    lib = b2rt.lib()
+    for name in ("room", "blob"):
+        g = np.load(os.path.join(golden, name + ".npz"))
+        v, t = np.ascontiguousarray(g["verts"], np.float32), np.ascontiguousarray(g["tris"], np.int32)
+        key = C.c_uint32()
+        assert lib.b2rt_bvhcache_key(v.ctypes.data_as(C.c_void_p), len(v), t.ctypes.data_as(C.c_void_p), len(t), None,
+                                     C.c_float(1.0e-5), 1, 8, b2rt.LAYOUT_COMPACT2, C.byref(key)) == 0
+        assert "%08x" % key.value == keys[name]["cache_key"]
+        # any ingredient changes the name
+        other = C.c_uint32()
+        lib.b2rt_bvhcache_key(v.ctypes.data_as(C.c_void_p), len(v), t.ctypes.data_as(C.c_void_p), len(t), None, C.c_float(1.0e-4), 1, 8,
+                              b2rt.LAYOUT_COMPACT2, C.byref(other))
+        assert other.value != key.value
+    buf = C.create_string_buffer(256)
+    assert lib.b2rt_bvhcache_path(os.path.join(golden, "bvhcache").encode(), int(keys["room"]["cache_key"], 16), buf, 256) == 0
+    path = buf.value.decode()
+    assert os.path.exists(path), "the reference-written cache file is not where the product looks for it"
+    bvh = b2rt.BVH.load(path)
+    g = np.load(os.path.join(golden, "room.npz"))
+    assert bvh.nodes.tobytes() == g["nodes"].tobytes() and bvh.woop.tobytes() == g["woop"].tobytes()
+    assert bvh.triIndex.tobytes() == g["triIndex"].tobytes()
+    out = str(tmp_path / "again.dat")
+    bvh.serialize(out)
+    assert open(out, "rb").read() == open(path, "rb").read()
+    assert lib.b2rt_bvhcache_path(b"x" * 300, 1, buf, 256) != 0          # a path that does not fit is refused
