@@ -149,6 +149,7 @@ def _workload_obj(name, tmpdir):
     h = C.c_void_p()
     if sl.b2rt_scene_generate(pkg.host.SCENE_KINDS[c["kind"]], c["tris"], C.c_uint64(c["seed"]), C.byref(h)) != 0:
         raise RuntimeError("scene generation failed")
+    os.makedirs(tmpdir, exist_ok=True)
     path = os.path.join(tmpdir, "%s-%d-%d.obj" % (c["kind"], c["tris"], c["seed"]))
     if not os.path.exists(path):
         tmp = path + ".%d.tmp" % os.getpid()

@@ -36,7 +36,11 @@ inline cudaError_t cudaBindTexture(size_t* offset, b2o_texref<T, 1>& tex, const 
 template <class T>
 inline cudaError_t cudaUnbindTexture(b2o_texref<T, 1>&) { return cudaSuccess; }
 
+#ifdef B2O_STATIC_TEXREF   /* several translation units include the declarations (route A: the reference's fetch_*.cu) */
+#define texture static __device__ ::b2o_texref
+#else
 #define texture __device__ ::b2o_texref
+#endif
 #define __ballot(p) __ballot_sync(__activemask(), (p))
 
 #endif
