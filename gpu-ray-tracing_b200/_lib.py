@@ -14,7 +14,7 @@ TRACE_WRITE_BARY = 2
 TRACE_STATS = 4
 TRACE_WATERTIGHT = 8
 COUNT_HITS_STATIC_MAX = 16 * 1024 * 1024
-TUNE_NO_STREAM, TUNE_GREEDY_WIDE, TUNE_L2_WINDOW = 1, 4, 8
+TUNE_NO_STREAM, TUNE_GREEDY_WIDE, TUNE_L2_WINDOW, TUNE_DEFAULT_CARVEOUT = 1, 4, 8, 16
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmin", "<f4"), ("d", "<f4", 3), ("tmax", "<f4")])
 RESULT_DTYPE = np.dtype([("id", "<i4"), ("t", "<f4"), ("padA", "<i4"), ("padB", "<i4")])

@@ -5,6 +5,8 @@
 #include <stdarg.h>
 
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <queue>
 #include <vector>
 
@@ -21,6 +23,19 @@ int setError(b2rt_ctx* ctx, int code, const char* fmt, ...)
     va_end(ap);
     if (ctx) ctx->lastError = buf; else g_createError = buf;
     return code;
+}
+
+int raiseSmemLimit(b2rt_ctx* ctx, const void* kern, size_t smem)
+{
+    static std::mutex lock;
+    static std::map<std::pair<int, const void*>, size_t> limit;
+    std::lock_guard<std::mutex> guard(lock);
+    size_t& cur = limit[std::make_pair(ctx->device, kern)];
+    if (smem > cur) {
+        B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cur = smem;
+    }
+    return B2RT_OK;
 }
 
 int ensureScratch(b2rt_ctx* ctx, size_t bytes)

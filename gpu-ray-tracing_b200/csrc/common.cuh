@@ -113,6 +113,11 @@ extern std::string g_createError;
         (ctx)->launches++;                                                                     \
     } while (0)
 
+// The dynamic shared-memory limit of a kernel is a property of the (device, kernel) pair for the whole process, and the same
+// kernel is launched with different sizes (the staged top of the tree depends on the BVH; several contexts may share a device):
+// it is only ever RAISED, under a process-wide lock (api.cu).
+int raiseSmemLimit(b2rt_ctx* ctx, const void* kern, size_t smem);
+
 // cudaFuncSetAttribute + the occupancy query, once per (kernel, shared-memory size) instead of on every launch
 template <class K>
 int kernelOccupancy(b2rt_ctx* ctx, K kern, int block, size_t smem, int* blocksPerSm)
@@ -121,8 +126,21 @@ int kernelOccupancy(b2rt_ctx* ctx, K kern, int block, size_t smem, int* blocksPe
     auto it = ctx->occupancy.find(key);
     if (it == ctx->occupancy.end()) {
         int n = 0;
-        B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        { const int rc = raiseSmemLimit(ctx, reinterpret_cast<const void*>(kern), smem); if (rc) return rc; }
         B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, block, smem));
+        if (n > 0 && !(ctx->cfg.tune & B2RT_TUNE_DEFAULT_CARVEOUT)) {
+            // Shared memory and L1 share 228 KB per SM.  Left to itself the driver carved out room for more CTAs than the
+            // registers allow (ncu: occupancy limit from shared memory 7 CTAs for a kernel that runs 4), i.e. ~64 KB of L1
+            // lost to shared memory nobody uses, with the traversal's L1 hit rate at 68 %.  Ask for what the resident CTAs
+            // need (their dynamic shared memory + 1 KB reserved per CTA) and leave the rest to L1.
+            const size_t need = (size_t)n * (smem + 1024);
+            int pct = (int)((need * 100 + 228 * 1024 - 1) / (228 * 1024));
+            if (pct > 100) pct = 100;
+            B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            int n2 = 0;
+            B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n2, kern, block, smem));
+            if (n2 < n) B2RT_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutDefault));
+        }
         it = ctx->occupancy.emplace(key, n).first;
     }
     *blocksPerSm = it->second;

@@ -617,7 +617,7 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
             // ... unless the collapsed tree is too deep for that kernel's stack (a degenerate caller-built BVH): stay binary
             const int rc = ensureWide(ctx);
             if (rc) return rc;
-            if (ctx->wideMaxDepth <= kWideMaxDepth) variant = 108;
+            if (ctx->wideMaxDepth <= kWideMaxDepth) variant = (numRays > (4 << 20)) ? 114 : 108;
         }
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);

@@ -40,6 +40,7 @@ struct WideParams {
 constexpr int kWideStack = 48;
 constexpr unsigned kFullMask = 0xffffffffu;
 
+
 // byte j of `word` as the float 1 + byte * 2^-15 (exact): one PRMT, no integer-to-float conversion
 // `one` must hold 0x3F800000 in a register the compiler cannot see through: PRMT takes one immediate, and it
 // should be the SELECTOR (otherwise four selector constants get re-materialised before every PRMT).
@@ -70,7 +71,7 @@ __device__ __forceinline__ void storeResultT(const WideParams& p, unsigned rayid
 // are the refill's atomic -> ray-load chain -- but a chunk is 16 samples of ONE primary ray, so 52 % of the C5 chunks are
 // entirely degenerate and a refill often fills no lane: 20 % more instructions, 40 % instead of 50 % of the warp slots
 // occupied, 3 265 -> 2 380 Mrays/s.
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, bool WT>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, bool WT, int CLAIM>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
     auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
@@ -98,7 +99,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
     unsigned octinv4 = 0;
     uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
     bool active = false;
+    constexpr int kClaim = CLAIM;           // rays a warp claims per atomic on the work counter (0: as many as it has idle lanes)
     bool poolEmpty = false;
+    unsigned blkBase = 0, blkLeft = 0;          // CLAIM: the warp's claimed block of rays (warp-uniform)
     unsigned long long stNodeIters = 0, stNodeLanes = 0, stTriIters = 0, stTriLanes = 0, stFetches = 0;
 
     // a fetched ray becomes this lane's ray -- or, degenerate (tmax < tmin, RayGenKernels.cu:223: it can hit nothing), is answered on the spot
@@ -132,16 +135,48 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         for (;;) {
             const unsigned maskT = __ballot_sync(kFullMask, !active);
             if (maskT == 0 || poolEmpty) break;
-            const unsigned numT = __popc(maskT);
+            unsigned numT = __popc(maskT);
+            unsigned base;
+            if (CLAIM > 0) {
+                // Block claims: one atomic on the work counter buys the warp `claim` consecutive rays; refills are served from the
+                // warp's own block, and the block's second half is pulled into L1 while the first is traced.  The refill chain
+                // "atomic (L2 round trip under contention) -> dependent ray load (DRAM: the batch streams through once)" held 13 % of
+                // the stall samples at 3 % of the instructions (profiles/r02_ncu_trace_wide_c5.md); 4 of 5 refills now find both
+                // the index and the ray at hand.  Measured on the C5 batch (profiles/r02_explore_c5_claims.log): 64 rays per claim +0.7 %,
+                // 128 +2.4 %, 256 +2.0 %; with the refill threshold at 26 instead of 24 another +0.6 %.  A warp holds up to claim - 1
+                // unstarted rays when the pool runs dry, which lengthens the tail of a frame-sized launch (C4 -14 %, C3 -10 %): used for
+                // batches of millions of rays only (launchTrace).
+                if (blkLeft == 0u) {
+                    unsigned b = 0;
+                    if (lane == 0) b = (unsigned)atomicAdd(p.warpCounter, kClaim);
+                    b = __shfl_sync(kFullMask, b, 0);
+                    if (STATS && lane == 0) stFetches++;
+                    if (b >= (unsigned)p.numRays) { poolEmpty = true; break; }
+                    blkBase = b;
+                    blkLeft = min((unsigned)kClaim, (unsigned)p.numRays - b);
+                    // rays [b + 32, b + claim): 32 bytes each, one 128-byte line per four rays
+#pragma unroll
+                    for (int k = 0; k < (kClaim - 32 + 127) / 128; k++) {
+                        const unsigned r = b + 32u + 4u * (lane + 32u * k);
+                        if (4 * (lane + 32 * k) < kClaim - 32 && r < (unsigned)p.numRays)
+                            asm volatile("prefetch.global.L1 [%0];" :: "l"(p.rays + 2 * (size_t)r));
+                    }
+                }
+                numT = min(numT, blkLeft);
+                base = blkBase;
+                blkBase += numT; blkLeft -= numT;
+            } else {
             const int leader = __ffs(maskT) - 1;
-            unsigned base = 0;
+            base = 0;
             if (lane == leader) base = (unsigned)atomicAdd(p.warpCounter, (int)numT);
             base = __shfl_sync(kFullMask, base, leader);
             if (STATS && lane == leader) stFetches++;
             poolEmpty = (base + numT >= (unsigned)p.numRays);
+            }
             if (!active) {
-                const unsigned idx = base + __popc(maskT & ((1u << lane) - 1u));
-                if (idx < (unsigned)p.numRays) {
+                const unsigned rank = __popc(maskT & ((1u << lane) - 1u));
+                const unsigned idx = base + rank;
+                if (rank < numT && idx < (unsigned)p.numRays) {
                     float4 o, d;
                     if (p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
                     else { o = ldg4(p.rays + 2 * (size_t)idx); d = ldg4(p.rays + 2 * (size_t)idx + 1); }
@@ -188,8 +223,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 unsigned hitmask = 0;
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
-                    // more than half of the nodes have <= 4 children, all in slots 0..3 (host/wide_bvh.cpp): skip the rest
-                    if (h == 1 && __float_as_uint(q1.w) == 0u) break;
+                    // (Round 1 skipped the upper half for nodes without children there.  With the SAH-optimal collapse 76 % of the
+                    //  nodes have more than four children, and at warp level the upper half ran in 19.1 M of 19.1 M steps anyway:
+                    //  removing the branch is +1.2 % on C5 and +1.6 % on C4, profiles/r02_explore_c5_opt.log.)
                     const unsigned loX = __float_as_uint(h ? q2.y : q2.x), loY = __float_as_uint(h ? q2.w : q2.z);
                     const unsigned loZ = __float_as_uint(h ? q3.y : q3.x), hiX = __float_as_uint(h ? q3.w : q3.z);
                     const unsigned hiY = __float_as_uint(h ? q4.y : q4.x), hiZ = __float_as_uint(h ? q4.w : q4.z);
@@ -227,6 +263,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             // Postponing (Ylitie et al. 2017, sec. 4.3): if fewer than 1/POSTPONE of the lanes that took this step
             // hold triangles, intersecting now would run the Woop test at a few lanes wide (ncu: 3.6 active threads per
             // triangle-loop instruction without it) -- park the group on the stack and keep traversing instead.
+            // The vote is repeated for every triangle of a group (voting once per group: -6 %).  POSTPONE sweep on C5, Mrays/s and
+            // node-loop / triangle-loop SIMD efficiency: 1/3 3 257 (66 % / 38 %), 1/4 3 337, 1/5 3 348 (75 % / 28 %), 1/6 3 336, 1/8 3 277,
+            // 1/16 3 047 (83 % / 16 %) -- profiles/r02_explore_c5_postpone.log; 1/5 also wins on C4 and C3.
             const int lanesHere = __popc(__activemask());
             if (LEAF == 1) {
                 // as trace.cu LEAF == 1: row 0 of the NEXT triangle of the group is requested before the current one is tested
@@ -332,10 +371,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, bool WT = false>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, int CLAIM, bool WT = false>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, WT>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, WT, CLAIM>;
     int blocksPerSm = 0;
     const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2);
     { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
@@ -369,21 +408,21 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0>
+template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0, int CLAIM = 0>
 static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_WATERTIGHT)
-        return any ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, true>(ctx, p, stream)
-                   : launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, true>(ctx, p, stream);
+        return any ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, true>(ctx, p, stream)
+                   : launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, true>(ctx, p, stream);
     if (flags & B2RT_TRACE_STATS)
-        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
-                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
-    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
-                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
-    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream)
-                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS>(ctx, p, stream);
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream);
 }
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
@@ -408,7 +447,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     // refill below 24 live lanes (the binary kernel and the reference use 20): a wide step is ~3x as many instructions as a
     // binary one, so an idle lane costs more; measured 12 / 16 / 20 / 24 / 28 on C5: 3 119 / 3 205 / 3 203 / 3 241 / 3 175,
     // C3: 3 086 (20) -> 3 153 (24)  (profiles/r01_explore_c{3,5}_wide_threshold.log)
-    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? 24 : ctx->cfg.fetch_threshold;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? (variant == 114 ? 26 : 24) : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
@@ -417,17 +456,21 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
     switch (variant) {
     default:
-    case 108: return launchWideFlags<256, 4, 3, 1, 8>(ctx, p, flags, stream);      // <= 64 regs, 32 warps/SM; triangle groups postponed below 1/3 of the
+    case 108: return launchWideFlags<256, 4, 5, 1, 8>(ctx, p, flags, stream);      // <= 64 regs, 32 warps/SM; triangle groups postponed below 1/5 of the
                                                                                    // lanes, look-ahead triangle loop, 8 stack entries in shared memory
+    case 114: return launchWideFlags<256, 4, 5, 1, 8, 128>(ctx, p, flags, stream); // 108 with 128-ray block claims: batches above 4 Mi rays
 #ifdef B2RT_EXPLORE
+    // shapes measured and not shipped; build with -DB2RT_EXPLORE to get them back
     case 100: return launchWideFlags<256, 3, 0>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM, no postponing
-    case 102: return launchWideFlags<256, 4, 0>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM, no postponing
-    case 104: return launchWideFlags<256, 4, 3>(ctx, p, flags, stream);   // postpone below 1/3
-    case 106: return launchWideFlags<256, 4, 3, 1>(ctx, p, flags, stream);  // 104 with the look-ahead triangle loop
-    case 109: return launchWideFlags<256, 4, 3, 1, 12>(ctx, p, flags, stream);  // 106 with 12 stack entries in shared memory
-    case 111: return launchWideFlags<256, 4, 0, 1, 8>(ctx, p, flags, stream);   // 108 without postponing
-    case 112: return launchWideFlags<256, 4, 2, 1, 8>(ctx, p, flags, stream);   // 108, postpone below 1/2
-    case 113: return launchWideFlags<512, 2, 3, 1, 8>(ctx, p, flags, stream);   // 108 in two 512-thread CTAs
+    case 104: return launchWideFlags<256, 4, 3>(ctx, p, flags, stream);   // postpone below 1/3, reference-shaped triangle loop
+    case 106: return launchWideFlags<256, 4, 3, 1>(ctx, p, flags, stream);     // 104 with the look-ahead triangle loop
+    case 107: return launchWideFlags<256, 4, 3, 1, 8>(ctx, p, flags, stream);  // round 1's default (postpone below 1/3)
+    case 109: return launchWideFlags<256, 4, 5, 1, 12>(ctx, p, flags, stream); // 12 stack entries in shared memory
+    case 111: return launchWideFlags<256, 4, 0, 1, 8>(ctx, p, flags, stream);  // 108 without postponing
+    case 113: return launchWideFlags<512, 2, 5, 1, 8>(ctx, p, flags, stream);  // 108 in two 512-thread CTAs
+    case 115: return launchWideFlags<256, 5, 5, 1, 8>(ctx, p, flags, stream);  // <= 48 regs (spills), 40 warps/SM: -7 %
+    case 132: return launchWideFlags<256, 4, 5, 1, 8, 64>(ctx, p, flags, stream);   // 64-ray claims
+    case 134: return launchWideFlags<256, 4, 5, 1, 8, 256>(ctx, p, flags, stream);  // 256-ray claims
 #endif
     }
 }

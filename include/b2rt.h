@@ -74,6 +74,8 @@ typedef struct {
 #define B2RT_TUNE_NO_STREAM      1u  /* rays / records through the normal cache policy instead of evict-first (ld.cs / st.cs) */
 #define B2RT_TUNE_GREEDY_WIDE    4u  /* 8-wide form: round-1 greedy top-down collapse instead of the SAH-optimal one; takes effect
                                         at the next b2rt_set_bvh */
+#define B2RT_TUNE_DEFAULT_CARVEOUT 16u /* leave the shared-memory / L1 split to the driver instead of asking for the resident CTAs' need;
+                                        takes effect for kernels not launched yet on this context */
 #define B2RT_TUNE_L2_WINDOW      8u  /* (opt-in) 8-wide kernel: persisting-L2 access window over the private wide arrays when they fit
                                         the device's set-aside; sets the device-wide cudaLimitPersistingL2CacheSize */
 
