@@ -1,5 +1,5 @@
 """Turn an .ncu-rep (ncu --set full) into the markdown summary kept under profiles/.
-usage: python tools/ncu_summary.py gpurun_out/prof_trace.ncu-rep profiles/rNN_name.md "title" [--traffic profiles/traffic.json key]"""
+usage: python tools/ncu_summary.py gpurun_out/prof_trace.ncu-rep profiles/rNN_name.md "title" [--traffic profiles/traffic.json key [rays per captured launch]]"""
 import csv, io, json, subprocess, sys
 
 METRICS = [
@@ -44,6 +44,14 @@ def main():
             return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
         per = [val(r, "dram__bytes_read.sum") + val(r, "dram__bytes_write.sum") for r in data]
         tj[key] = {"dram_bytes_per_launch": sum(per) / len(per), "launches": len(per), "source": out}
+        # executed warp-instructions per launched ray (bench.py's issue roofline): rays of the captured launch = 4th argument
+        if len(sys.argv) > k + 3:
+            rays = float(sys.argv[k + 3])
+            inst = [float(r[col["smsp__inst_executed.sum"]].replace(",", "")) for r in data]
+            tj[key]["warp_inst_per_ray"] = sum(inst) / len(inst) / rays
+            tj[key]["rays_per_captured_launch"] = rays
+            tj[key]["issue_active_per_cycle"] = float(data[0][col["smsp__issue_active.avg.per_cycle_active"]])
+            tj[key]["threads_per_inst"] = float(data[0][col["smsp__thread_inst_executed_per_inst_executed.ratio"]])
         json.dump(tj, open(path, "w"), indent=1)
     print(open(out).read())
 
