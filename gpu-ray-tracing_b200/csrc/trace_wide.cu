@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 // the index and the ray at hand.  Measured on the C5 batch (profiles/r02_explore_c5_claims.log): 64 rays per claim +0.7 %,
                 // 128 +2.4 %, 256 +2.0 %; with the refill threshold at 26 instead of 24 another +0.6 %.  A warp holds up to claim - 1
                 // unstarted rays when the pool runs dry, which lengthens the tail of a frame-sized launch (C4 -14 %, C3 -10 %): used for
-                // batches of millions of rays only (launchTrace).
+                // batches above 24 Mi rays only (launchTrace).
                 if (blkLeft == 0u) {
                     unsigned b = 0;
                     if (lane == 0) b = (unsigned)atomicAdd(p.warpCounter, kClaim);
@@ -458,7 +458,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     default:
     case 108: return launchWideFlags<256, 4, 5, 1, 8>(ctx, p, flags, stream);      // <= 64 regs, 32 warps/SM; triangle groups postponed below 1/5 of the
                                                                                    // lanes, look-ahead triangle loop, 8 stack entries in shared memory
-    case 114: return launchWideFlags<256, 4, 5, 1, 8, 128>(ctx, p, flags, stream); // 108 with 128-ray block claims: batches above 4 Mi rays
+    case 114: return launchWideFlags<256, 4, 5, 1, 8, 128>(ctx, p, flags, stream); // 108 with 128-ray block claims: batches above 24 Mi rays
 #ifdef B2RT_EXPLORE
     // shapes measured and not shipped; build with -DB2RT_EXPLORE to get them back
     case 100: return launchWideFlags<256, 3, 0>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM, no postponing

@@ -29,7 +29,11 @@ def main():
     sort_batches = "--sorted" in sys.argv      # Morton-sort every secondary batch first (RayBuffer::mortonSort), untimed
     ctx = b2rt.Context.get(0)
     scene, bvh = wl.build_scene_and_bvh(name, log=lambda s: print(s, flush=True))
-    frame = wl.Frame(name, scene, bvh.arrays(), "cuda:0", ctx)
+    shard = (0, 1)
+    for a in sys.argv:
+        if a.startswith("--shard="):           # --shard=r,w : rank r's share of a sharded workload (c5), traced on this one GPU
+            shard = tuple(int(x) for x in a.split("=")[1].split(","))
+    frame = wl.Frame(name, scene, bvh.arrays(), "cuda:0", ctx, shard=shard)
     counted = frame.counted_rays()
     if sort_batches:
         for rb, _ in frame.batches:

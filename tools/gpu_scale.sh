@@ -1,9 +1,18 @@
 #!/bin/bash
-# usage: gpu_scale.sh N   -- bench.py at N ranks (torchrun), C2 weak scaling and C5 strong scaling
+# usage: gpu_scale.sh N   -- bench.py (default workload c5, strong scaling) at N ranks, as the driver launches it
 N=$1
 mkdir -p gpurun_out
-run() { timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N "$@"; }
-run --steps 100 --warmup 5 > gpurun_out/scale_c2_n$N.json 2> gpurun_out/scale_c2_n$N.err; echo "rc=$?" >> gpurun_out/scale_c2_n$N.err
-run --steps 10 --warmup 3 --workload c5 > gpurun_out/scale_c5_n$N.json 2> gpurun_out/scale_c5_n$N.err; echo "rc=$?" >> gpurun_out/scale_c5_n$N.err
-tail -n 3 gpurun_out/scale_c2_n$N.err gpurun_out/scale_c5_n$N.err
-cat gpurun_out/scale_c2_n$N.json gpurun_out/scale_c5_n$N.json | cut -c1-400
+if [ "$N" = "1" ]; then
+  timeout 900 python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/scale_n$N.json 2> gpurun_out/scale_n$N.err
+else
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/scale_n$N.json 2> gpurun_out/scale_n$N.err
+fi
+echo "rc=$?" >> gpurun_out/scale_n$N.err
+grep "^rank\|rc=\|Error\|error" gpurun_out/scale_n$N.err | sort | head -12
+python - <<PY
+import json
+for l in open("gpurun_out/scale_n$N.json"):
+    if l.startswith("{"):
+        d = json.loads(l)
+        print({k: d.get(k) for k in ("value", "n_gpus", "ms_per_step", "scaling")}, "with_gather", d.get("with_gather", {}).get("value"), "e2e", d["e2e"]["value"], "frame", d["e2e"].get("frame", {}).get("value"), "hits", d.get("hits_gathered"))
+PY
