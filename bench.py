@@ -47,6 +47,17 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries exactly ONE line, the JSON result: everything else a library prints there (NCCL's version banner, the reference
+# launcher's grid print) goes to stderr.  File descriptor 1 is pointed at stderr for the run; emit() writes to the real stdout.
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -313,7 +324,7 @@ def reference_arm(args):
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -708,7 +719,7 @@ def product_arm(args):
         except Exception as e:          # the baseline must never take the bench line down with it
             line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": procs, "kind": "reference", "sample": "failed: %s" % e}
     line["bench_wall_s"] = time.time() - T_START
-    print(json.dumps(line), flush=True)
+    emit(line)
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()
