@@ -53,6 +53,11 @@ _REAL_STDOUT = os.fdopen(os.dup(1), "w")
 os.dup2(2, 1)
 
 
+def _nbytes(a):
+    """bytes of a numpy array or a torch tensor (the broadcast BVH arrays stay on the device under nccl)"""
+    return int(a.numel() * a.element_size()) if hasattr(a, "element_size") else int(a.nbytes)
+
+
 def emit(line):
     _REAL_STDOUT.write(json.dumps(line) + "\n")
     _REAL_STDOUT.flush()
@@ -598,7 +603,7 @@ def product_arm(args):
         pass
     traffic = prof.get("dram_bytes_per_launch")
     # which kernel the library's default policy launches for these batches (trace.cu:launchTrace)
-    wide = (args.variant >= 100) or (args.variant < 0 and float(arrays["nodes"].nbytes + arrays["woop"].nbytes) > float(48 << 20))
+    wide = (args.variant >= 100) or (args.variant < 0 and float(_nbytes(arrays["nodes"]) + _nbytes(arrays["woop"])) > float(48 << 20))
     clocks = sampler.summary()
     sm_hz = (clocks["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)) * 1e6
     sm_count = ctx.sm_count()
@@ -633,7 +638,7 @@ def product_arm(args):
         "config": bench_config(name, ws),
         "detail": {"rays_per_step_per_gpu": launched, "counted_rays_per_step": int(counted_all), "launched_rays_per_step": int(launched_all),
                    "batches_per_step": n_launch_step,
-                   "bvh": "%d nodes, %d Woop rows" % (arrays["nodes"].size // 16, arrays["woop"].size // 4)},
+                   "bvh": "%d nodes, %d Woop rows" % (_nbytes(arrays["nodes"]) // 64, _nbytes(arrays["woop"]) // 16)},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
                 "steps": e2e_steps, "ms_per_step": e2e_ms_max / e2e_steps,
                 "api": "b2rt_trace_host_begin per batch + b2rt_trace_host_end per step (pinned host rays in, host hit records out)",

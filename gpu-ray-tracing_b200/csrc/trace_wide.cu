@@ -71,15 +71,30 @@ __device__ __forceinline__ void storeResultT(const WideParams& p, unsigned rayid
 // are the refill's atomic -> ray-load chain -- but a chunk is 16 samples of ONE primary ray, so 52 % of the C5 chunks are
 // entirely degenerate and a refill often fills no lane: 20 % more instructions, 40 % instead of 50 % of the warp slots
 // occupied, 3 265 -> 2 380 Mrays/s.
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, bool WT, int CLAIM>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, bool WT, int CLAIM, int OPT>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideParams p)
 {
+    extern __shared__ uint2 s_wideStack[];
+    // OPT bit 1 (MASK): a child's (bits, bit index) byte is pulled out with one PRMT and shifted with a wrapping shift: 4 instead
+    //           of 5 integer operations per child.  C5 3 495 -> 3 524..3 530 Mrays/s (+0.9 %).
+    // (OPT bit 0 was HOLD: a lane whose turned-away group is all it has kept it in registers instead of pushing and popping it
+    //  every iteration, and requested a group's first row only after the vote.  Same traversal (TRV / IST identical), fewer stack
+    //  operations, 48 more static instructions -- and C5 3 495 -> 3 366: removed.  profiles/r02_explore_park_mask.log)
+    constexpr bool MASK = (OPT & 2) != 0;
+    // OPT bit 2 (PARK, LEAF == 1 only): a triangle group the vote turns away goes to a one-entry waiting room of its own (shared
+    //           memory) instead of the traversal stack, and is offered again at EVERY triangle phase in which the lane has no
+    //           fresh group; the lane keeps traversing meanwhile.  (A group pushed on the stack is not seen again before everything
+    //           above it is done; a group popped from the stack and turned away again makes the lane spin on it.)  Node-loop SIMD
+    //           efficiency on C5 77 -> 84 % at the same threshold; with the threshold at 1/4: 83 % / 32 %, C5 3 530 -> 3 556, C4
+    //           612 -> 624..628, C3 3 330 -> 3 379..3 393, an 8 Mi-ray shard of C5 3 213 -> 3 251 (same log).
+    constexpr bool PARK = (OPT & 4) != 0 && LEAF == 1 && POSTPONE > 0;
+    uint2* s_park = s_wideStack + SSLOTS * BLOCK + threadIdx.x;
+    bool parked = false;
     auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
     const int lane = threadIdx.x & 31;
     // Traversal stack: the first SSLOTS entries in shared memory (slot k of this thread at s_stack[k * BLOCK]: consecutive
     // threads, consecutive 8-byte words), the rest in local memory.  Entirely in local memory (SSLOTS == 0) the stack moved
     // 23 GB through L1 per 64 Mi-ray launch and its pops held 6 % of the stall samples (ncu source page, C5).
-    extern __shared__ uint2 s_wideStack[];
     uint2* s_stack = s_wideStack + threadIdx.x;
     uint2 lstack[kWideStack];
     auto push = [&](int& sp_, const uint2 v) {
@@ -119,7 +134,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         octinv4 = ((idirx < 0.0f ? 0u : 4u) | (idiry < 0.0f ? 0u : 2u) | (idirz < 0.0f ? 0u : 1u)) * 0x01010101u;
         G = make_uint2(0u, 0x80000000u);               // the root, as a group of one
         T = make_uint2(0u, 0u);
-        sp = 0; hitIndex = -1;
+        sp = 0; hitIndex = -1; parked = false;
         if (BARY) { hitU = 0.0f; hitV = 0.0f; }
         active = true;
     };
@@ -237,6 +252,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                     const unsigned innerMask4 = (isInner4 >> 4) * 0xFFu;
                     const unsigned bitIndex4 = (meta4 ^ (octinv4 & innerMask4)) & 0x1F1F1F1Fu;
                     const unsigned childBits4 = (meta4 >> 5) & 0x07070707u;
+                    const unsigned m4 = meta4 ^ (octinv4 & innerMask4);         // per byte: bits 0-4 the bit index, bits 5-7 the child's bits
 #define B2RT_WIDE_CHILD(J)                                                                                          \
                     {                                                                                               \
                         const float t0x = __fmaf_rn(byteToUnitFloat<J>(nearX, one), ax, bx);                           \
@@ -247,7 +263,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                         const float t1z = __fmaf_rn(byteToUnitFloat<J>(farZ, one) , az, bz);                            \
                         const float cmin = fmax3(t0x, t0y, fmaxf(t0z, tmin));                                      \
                         const float cmax = fmin3(t1x, t1y, fminf(t1z, WT ? cullT : hitT));                                      \
-                        if (WT ? watertightOverlap(cmin, cmax, wslack) : (cmin <= cmax)) hitmask |= ((childBits4 >> (8 * J)) & 0xFFu) << ((bitIndex4 >> (8 * J)) & 0xFFu); \
+                        if (WT ? watertightOverlap(cmin, cmax, wslack) : (cmin <= cmax)) {                          \
+                            if (MASK) { const unsigned m = __byte_perm(m4, 0u, 0x4440u + J); hitmask |= __funnelshift_l(0u, m >> 5, m); } \
+                            else hitmask |= ((childBits4 >> (8 * J)) & 0xFFu) << ((bitIndex4 >> (8 * J)) & 0xFFu);       \
+                        }                                                                                           \
                     }
                     B2RT_WIDE_CHILD(0) B2RT_WIDE_CHILD(1) B2RT_WIDE_CHILD(2) B2RT_WIDE_CHILD(3)
 #undef B2RT_WIDE_CHILD
@@ -265,7 +284,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             // triangle-loop instruction without it) -- park the group on the stack and keep traversing instead.
             // The vote is repeated for every triangle of a group (voting once per group: -6 %).  POSTPONE sweep on C5, Mrays/s and
             // node-loop / triangle-loop SIMD efficiency: 1/3 3 257 (66 % / 38 %), 1/4 3 337, 1/5 3 348 (75 % / 28 %), 1/6 3 336, 1/8 3 277,
-            // 1/16 3 047 (83 % / 16 %) -- profiles/r02_explore_c5_postpone.log; 1/5 also wins on C4 and C3.
+            // 1/16 3 047 (83 % / 16 %) -- profiles/r02_explore_c5_postpone.log; 1/5 also wins on C4 and C3.  With PARK (turned-away
+            // groups wait in a room of their own and the lane traverses on) the balance moves: 1/5 3 523 (84 % / 29 %), 1/4 3 557
+            // (83 % / 32 %), 1/3 3 548 (79 % / 39 %), 1/2 3 342 (69 % / 52 %) -- profiles/r02_explore_park_mask.log; shipped: 1/4.
+            if (PARK && parked && T.y == 0u) { T = *s_park; parked = false; }      // no fresh group: offer the parked one
             const int lanesHere = __popc(__activemask());
             if (LEAF == 1) {
                 // as trace.cu LEAF == 1: row 0 of the NEXT triangle of the group is requested before the current one is tested
@@ -273,6 +295,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 int tri = (int)T.x + (T.y ? __ffs(T.y) - 1 : 0);
                 float4 v00 = ldg4(p.woop + (size_t)tri * 3);
                 while (T.y != 0u) {
+                    if (PARK) {
+                        if (__popc(__activemask()) * POSTPONE < lanesHere) {
+                            if (!parked) { *s_park = T; parked = true; break; }
+                            if (sp < p.pushLimit) { push(sp, T); break; }
+                        }
+                    } else
                     if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < p.pushLimit) {
                         push(sp, T);
                         break;
@@ -296,7 +324,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                         hitT = t; hitIndex = tri;
                         if (WT) cullT = watertightCull(t);
                         if (BARY) { hitU = u; hitV = v; }
-                        if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; }
+                        if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; parked = false; }
                     }
                     v00 = n00; tri = ntri;
                 }
@@ -345,7 +373,10 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 
             // ---- next group ---------------------------------------------------------------------
             if (G.y <= 0x00FFFFFFu) {
-                if (sp == 0) { active = false; break; }
+                if (sp == 0) {
+                    if (PARK && parked) { G = *s_park; parked = false; }       // all that is left: comes back like a popped group
+                    else { active = false; break; }
+                } else
                 G = pop(sp);
             }
             if (__popc(__activemask()) < threshold) break;          // dynamic fetch: refill the idle lanes
@@ -371,12 +402,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
 // ---------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, int CLAIM, bool WT = false>
+template <bool ANY_HIT, bool BARY, bool STATS, int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF, int SSLOTS, int CLAIM, int OPT, bool WT = false>
 static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
-    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, WT, CLAIM>;
+    auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, WT, CLAIM, OPT>;
     int blocksPerSm = 0;
-    const size_t smem = (size_t)SSLOTS * BLOCK * sizeof(uint2);
+    const size_t smem = (size_t)(SSLOTS + ((OPT & 4) ? 1 : 0)) * BLOCK * sizeof(uint2);
     { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
@@ -408,21 +439,21 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
     return B2RT_OK;
 }
 
-template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0, int CLAIM = 0>
+template <int BLOCK, int MIN_BLOCKS, int POSTPONE, int LEAF = 0, int SSLOTS = 0, int CLAIM = 0, int OPT = 0>
 static int launchWideFlags(b2rt_ctx* ctx, WideParams& p, unsigned flags, cudaStream_t stream)
 {
     const bool any = (flags & B2RT_TRACE_ANY_HIT) != 0;
     const bool bary = (flags & B2RT_TRACE_WRITE_BARY) != 0;
     if (flags & B2RT_TRACE_WATERTIGHT)
-        return any ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, true>(ctx, p, stream)
-                   : launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, true>(ctx, p, stream);
+        return any ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT, true>(ctx, p, stream)
+                   : launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT, true>(ctx, p, stream);
     if (flags & B2RT_TRACE_STATS)
-        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream)
-                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream);
-    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream)
-                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream);
-    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream)
-                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM>(ctx, p, stream);
+        return any ? launchWideOne<true, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT>(ctx, p, stream)
+                   : launchWideOne<false, true, true, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT>(ctx, p, stream);
+    if (any) return bary ? launchWideOne<true, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT>(ctx, p, stream)
+                         : launchWideOne<true, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT>(ctx, p, stream);
+    return bary ? launchWideOne<false, true, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT>(ctx, p, stream)
+                : launchWideOne<false, false, false, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, CLAIM, OPT>(ctx, p, stream);
 }
 
 int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays, unsigned flags, int variant,
@@ -447,7 +478,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     // refill below 24 live lanes (the binary kernel and the reference use 20): a wide step is ~3x as many instructions as a
     // binary one, so an idle lane costs more; measured 12 / 16 / 20 / 24 / 28 on C5: 3 119 / 3 205 / 3 203 / 3 241 / 3 175,
     // C3: 3 086 (20) -> 3 153 (24)  (profiles/r01_explore_c{3,5}_wide_threshold.log)
-    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? (variant == 114 ? 26 : 24) : ctx->cfg.fetch_threshold;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148) ? 26 : 24) : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
@@ -456,11 +487,19 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
     switch (variant) {
     default:
-    case 108: return launchWideFlags<256, 4, 5, 1, 8>(ctx, p, flags, stream);      // <= 64 regs, 32 warps/SM; triangle groups postponed below 1/5 of the
-                                                                                   // lanes, look-ahead triangle loop, 8 stack entries in shared memory
-    case 114: return launchWideFlags<256, 4, 5, 1, 8, 128>(ctx, p, flags, stream); // 108 with 128-ray block claims: batches above 24 Mi rays
+    case 108: return launchWideFlags<256, 4, 4, 1, 8, 0, 6>(ctx, p, flags, stream);    // <= 64 regs, 32 warps/SM; look-ahead triangle loop, 8 stack entries in
+                                                                                       // shared memory; triangle groups turned away below 1/4 of the lanes wait in a
+                                                                                       // one-entry room of their own (PARK), hit mask through PRMT (MASK)
+    case 114: return launchWideFlags<256, 4, 4, 1, 8, 128, 6>(ctx, p, flags, stream);  // 108 with 128-ray block claims: batches above 24 Mi rays
 #ifdef B2RT_EXPLORE
     // shapes measured and not shipped; build with -DB2RT_EXPLORE to get them back
+    case 118: return launchWideFlags<256, 4, 5, 1, 8>(ctx, p, flags, stream);            // variant 108 until the end of round 2: groups pushed on the stack, threshold 1/5
+    case 124: return launchWideFlags<256, 4, 5, 1, 8, 128>(ctx, p, flags, stream);       // variant 114 until then
+    case 142: return launchWideFlags<256, 4, 5, 1, 8, 128, 2>(ctx, p, flags, stream);    // 124 + MASK
+    case 145: return launchWideFlags<256, 4, 5, 1, 8, 128, 6>(ctx, p, flags, stream);    // 124 + MASK + PARK, threshold 1/5
+    case 147: return launchWideFlags<256, 4, 3, 1, 8, 128, 6>(ctx, p, flags, stream);    //   ... 1/3
+    case 148: return launchWideFlags<256, 4, 2, 1, 8, 128, 6>(ctx, p, flags, stream);    //   ... 1/2
+    case 150: return launchWideFlags<256, 4, 3, 1, 8, 0, 6>(ctx, p, flags, stream);      // 108 with the threshold at 1/3
     case 100: return launchWideFlags<256, 3, 0>(ctx, p, flags, stream);   // <= 80 regs, 24 warps/SM, no postponing
     case 104: return launchWideFlags<256, 4, 3>(ctx, p, flags, stream);   // postpone below 1/3, reference-shaped triangle loop
     case 106: return launchWideFlags<256, 4, 3, 1>(ctx, p, flags, stream);     // 104 with the look-ahead triangle loop

@@ -215,9 +215,19 @@ class CudaBVH:
             arrays = bvh        # dict with nodes / woop / triIndex (e.g. read from a bvhcache file)
         self.m_layout = int(arrays.get("layout", layout)) if layout == LAYOUT_COMPACT2 else int(layout)
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-        self.m_nodes = torch.from_numpy(np.ascontiguousarray(arrays["nodes"], np.float32).copy()).to(self.device)
-        self.m_triWoop = torch.from_numpy(np.ascontiguousarray(arrays["woop"], np.float32).copy()).to(self.device)
-        self.m_triIndex = torch.from_numpy(np.ascontiguousarray(arrays["triIndex"], np.int32).copy()).to(self.device)
+        self.m_nodes = self._upload(arrays["nodes"], np.float32)
+        self.m_triWoop = self._upload(arrays["woop"], np.float32)
+        self.m_triIndex = self._upload(arrays["triIndex"], np.int32)
+
+    def _upload(self, array, dtype):
+        """numpy (or anything numpy reads) -> a fresh device tensor; a torch tensor already on the device is taken as it is
+        (multigpu.broadcast_bvh leaves the broadcast arrays there)."""
+        if isinstance(array, torch.Tensor):
+            want = torch.float32 if dtype == np.float32 else torch.int32
+            if array.dtype != want:
+                raise TypeError("CudaBVH: device array of dtype %s, expected %s" % (array.dtype, want))
+            return array.contiguous().reshape(-1).to(self.device)
+        return torch.from_numpy(np.ascontiguousarray(array, dtype).copy()).to(self.device)
 
     @classmethod
     def fromSceneOnDevice(cls, scene, arrays, ctx=None, device=None):

@@ -37,7 +37,8 @@ def _comm_device(device):
 
 def broadcast_bvh(arrays, device, src=0):
     """Replicate the Compact2 arrays of rank `src` on every rank.  `arrays` is a dict with numpy
-    nodes / woop / triIndex on `src` and may be None elsewhere.  Returns the dict on every rank."""
+    nodes / woop / triIndex on `src` and may be None elsewhere.  Returns the dict on every rank: device tensors under
+    nccl, numpy arrays under gloo and for a single rank."""
     rank, ws = world()
     if ws == 1:
         return arrays
@@ -56,7 +57,9 @@ def broadcast_bvh(arrays, device, src=0):
         else:
             t = torch.empty(n, dtype=dt, device=cd)
         dist.broadcast(t, src)
-        out[key] = t.cpu().numpy()
+        # nccl: the arrays stay on the device -- CudaBVH takes device tensors as they are, so no rank pulls the BVH back to
+        # the host to upload it again (1.2 GB on the 6.5 M-triangle scene); gloo (CPU tests): numpy, as on rank `src`
+        out[key] = t if t.is_cuda else t.numpy()
     return out
 
 
