@@ -85,11 +85,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
     //           memory) instead of the traversal stack, and is offered again at EVERY triangle phase in which the lane has no
     //           fresh group; the lane keeps traversing meanwhile.  (A group pushed on the stack is not seen again before everything
     //           above it is done; a group popped from the stack and turned away again makes the lane spin on it.)  Node-loop SIMD
-    //           efficiency on C5 77 -> 84 % at the same threshold; with the threshold at 1/4: 83 % / 32 %, C5 3 530 -> 3 556, C4
-    //           612 -> 624..628, C3 3 330 -> 3 379..3 393, an 8 Mi-ray shard of C5 3 213 -> 3 251 (same log).
+    //           efficiency on C5 77 -> 84 % at the same threshold; with the threshold at 1/4: 83 % / 32 %, C5 3 530 -> 3 556..3 585, C4
+    //           612 -> 624..628, C3 3 330 -> 3 379..3 438, an 8 Mi-ray shard of C5 3 213 -> 3 251 (same log).
     constexpr bool PARK = (OPT & 4) != 0 && LEAF == 1 && POSTPONE > 0;
+    constexpr int kParkDepth = (OPT & 8) ? 2 : 1;       // OPT bit 3: two waiting-room entries per lane (10 M of the 15 M warp iterations of a C5
+                                                        // launch still push one lane's group because its room is taken -- but the indexed room
+                                                        // costs more than those pushes: C5 3 585 -> 3 480)
     uint2* s_park = s_wideStack + SSLOTS * BLOCK + threadIdx.x;
-    bool parked = false;
+    int parked = 0;                                     // groups of this lane in the waiting room
     auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
     const int lane = threadIdx.x & 31;
     // Traversal stack: the first SSLOTS entries in shared memory (slot k of this thread at s_stack[k * BLOCK]: consecutive
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         octinv4 = ((idirx < 0.0f ? 0u : 4u) | (idiry < 0.0f ? 0u : 2u) | (idirz < 0.0f ? 0u : 1u)) * 0x01010101u;
         G = make_uint2(0u, 0x80000000u);               // the root, as a group of one
         T = make_uint2(0u, 0u);
-        sp = 0; hitIndex = -1; parked = false;
+        sp = 0; hitIndex = -1; parked = 0;
         if (BARY) { hitU = 0.0f; hitV = 0.0f; }
         active = true;
     };
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             // 1/16 3 047 (83 % / 16 %) -- profiles/r02_explore_c5_postpone.log; 1/5 also wins on C4 and C3.  With PARK (turned-away
             // groups wait in a room of their own and the lane traverses on) the balance moves: 1/5 3 523 (84 % / 29 %), 1/4 3 557
             // (83 % / 32 %), 1/3 3 548 (79 % / 39 %), 1/2 3 342 (69 % / 52 %) -- profiles/r02_explore_park_mask.log; shipped: 1/4.
-            if (PARK && parked && T.y == 0u) { T = *s_park; parked = false; }      // no fresh group: offer the parked one
+            if (PARK && parked && T.y == 0u) { parked--; T = s_park[(kParkDepth == 1 ? 0 : parked) * BLOCK]; }      // no fresh group: offer the parked one
             const int lanesHere = __popc(__activemask());
             if (LEAF == 1) {
                 // as trace.cu LEAF == 1: row 0 of the NEXT triangle of the group is requested before the current one is tested
@@ -297,7 +300,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 while (T.y != 0u) {
                     if (PARK) {
                         if (__popc(__activemask()) * POSTPONE < lanesHere) {
-                            if (!parked) { *s_park = T; parked = true; break; }
+                            if (parked < kParkDepth) { s_park[(kParkDepth == 1 ? 0 : parked) * BLOCK] = T; parked++; break; }
                             if (sp < p.pushLimit) { push(sp, T); break; }
                         }
                     } else
@@ -324,7 +327,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                         hitT = t; hitIndex = tri;
                         if (WT) cullT = watertightCull(t);
                         if (BARY) { hitU = u; hitV = v; }
-                        if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; parked = false; }
+                        if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; parked = 0; }
                     }
                     v00 = n00; tri = ntri;
                 }
@@ -374,7 +377,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             // ---- next group ---------------------------------------------------------------------
             if (G.y <= 0x00FFFFFFu) {
                 if (sp == 0) {
-                    if (PARK && parked) { G = *s_park; parked = false; }       // all that is left: comes back like a popped group
+                    if (PARK && parked) { parked--; G = s_park[(kParkDepth == 1 ? 0 : parked) * BLOCK]; }       // all that is left: comes back like a popped group
                     else { active = false; break; }
                 } else
                 G = pop(sp);
@@ -407,7 +410,7 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
     auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, WT, CLAIM, OPT>;
     int blocksPerSm = 0;
-    const size_t smem = (size_t)(SSLOTS + ((OPT & 4) ? 1 : 0)) * BLOCK * sizeof(uint2);
+    const size_t smem = (size_t)(SSLOTS + ((OPT & 4) ? ((OPT & 8) ? 2 : 1) : 0)) * BLOCK * sizeof(uint2);
     { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
@@ -478,7 +481,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     // refill below 24 live lanes (the binary kernel and the reference use 20): a wide step is ~3x as many instructions as a
     // binary one, so an idle lane costs more; measured 12 / 16 / 20 / 24 / 28 on C5: 3 119 / 3 205 / 3 203 / 3 241 / 3 175,
     // C3: 3 086 (20) -> 3 153 (24)  (profiles/r01_explore_c{3,5}_wide_threshold.log)
-    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148) ? 26 : 24) : ctx->cfg.fetch_threshold;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148 || variant == 160 || variant == 162) ? 26 : 24) : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
@@ -493,6 +496,9 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     case 114: return launchWideFlags<256, 4, 4, 1, 8, 128, 6>(ctx, p, flags, stream);  // 108 with 128-ray block claims: batches above 24 Mi rays
 #ifdef B2RT_EXPLORE
     // shapes measured and not shipped; build with -DB2RT_EXPLORE to get them back
+    case 160: return launchWideFlags<256, 4, 4, 1, 8, 128, 14>(ctx, p, flags, stream);   // 114 with two waiting-room entries: C5 3 585 -> 3 480, C3 3 434 -> 3 344
+    case 161: return launchWideFlags<256, 4, 4, 1, 8, 0, 14>(ctx, p, flags, stream);     // 108 with two
+    case 162: return launchWideFlags<256, 4, 3, 1, 8, 128, 14>(ctx, p, flags, stream);   //   ... threshold 1/3
     case 118: return launchWideFlags<256, 4, 5, 1, 8>(ctx, p, flags, stream);            // variant 108 until the end of round 2: groups pushed on the stack, threshold 1/5
     case 124: return launchWideFlags<256, 4, 5, 1, 8, 128>(ctx, p, flags, stream);       // variant 114 until then
     case 142: return launchWideFlags<256, 4, 5, 1, 8, 128, 2>(ctx, p, flags, stream);    // 124 + MASK
