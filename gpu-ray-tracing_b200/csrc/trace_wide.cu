@@ -212,7 +212,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         }
         const int threshold = poolEmpty ? 0 : p.fetchThreshold;
 
+#ifndef B2RT_LOOP_WHILE
+        if (active) for (;;) {
+#else
         while (active) {
+#endif
             // ---- node step ----------------------------------------------------------------------
             if (G.y > 0x00FFFFFFu) {
                 if (STATS) { const unsigned am = __activemask(); stNodeLanes++; if (lane == __ffs(am) - 1) stNodeIters++; }
