@@ -301,25 +301,28 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 // (the hit mask names it), Woop test without early-outs -- the same operations in the same order
                 int tri = (int)T.x + (T.y ? __ffs(T.y) - 1 : 0);
                 float4 v00 = ldg4(p.woop + (size_t)tri * 3);
-                while (T.y != 0u) {
+                // true: the group (what is left of it) was turned away and put aside
+                auto turnedAway = [&]() -> bool {
                     if (PARK) {
                         if (__popc(__activemask()) * POSTPONE < lanesHere) {
-                            if (parked < kParkDepth) { s_park[(kParkDepth == 1 ? 0 : parked) * BLOCK] = T; parked++; break; }
-                            if (sp < p.pushLimit) { push(sp, T); break; }
+                            if (parked < kParkDepth) { s_park[(kParkDepth == 1 ? 0 : parked) * BLOCK] = T; parked++; return true; }
+                            if (sp < p.pushLimit) { push(sp, T); return true; }
                         }
-                    } else
-                    if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < p.pushLimit) {
-                        push(sp, T);
-                        break;
+                        return false;
                     }
+                    if (POSTPONE > 0 && __popc(__activemask()) * POSTPONE < lanesHere && sp < p.pushLimit) { push(sp, T); return true; }
+                    return false;
+                };
+                // tests triangle `cur` (row 0 in `c00`), requests row 0 of the group's next triangle into `n00`
+                auto triStep = [&](const int cur, const float4& c00, int& nxt, float4& n00) {
                     if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
                     T.y &= T.y - 1u;
-                    const int ntri = (int)T.x + (T.y ? __ffs(T.y) - 1 : 0);
-                    const float4* w = p.woop + (size_t)tri * 3;
-                    const float4 n00 = ldg4(p.woop + (size_t)ntri * 3);
+                    nxt = (int)T.x + (T.y ? __ffs(T.y) - 1 : 0);
+                    const float4* w = p.woop + (size_t)cur * 3;
+                    n00 = ldg4(p.woop + (size_t)nxt * 3);
                     const float4 v11 = ldg4(w + 1), v22 = ldg4(w + 2);
-                    const float Oz = woopPlane(-origx, -origy, -origz, v00);
-                    const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
+                    const float Oz = woopPlane(-origx, -origy, -origz, c00);
+                    const float invDz = rcp_approx(woopDot(dirx, diry, dirz, c00));
                     const float t = fmulFtz(Oz, invDz);
                     const float Ox = woopPlane(origx, origy, origz, v11);
                     const float Dx = woopDot(dirx, diry, dirz, v11);
@@ -327,12 +330,28 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                     const float Oy = woopPlane(origx, origy, origz, v22);
                     const float Dy = woopDot(dirx, diry, dirz, v22);
                     const float v = ffmaFtz(t, Dy, Oy);
-                    if (woopAccept<WT>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, tri, hitIndex, p.triIndex)) {
-                        hitT = t; hitIndex = tri;
+                    if (woopAccept<WT>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, cur, hitIndex, p.triIndex)) {
+                        hitT = t; hitIndex = cur;
                         if (WT) cullT = watertightCull(t);
                         if (BARY) { hitU = u; hitV = v; }
                         if (ANY_HIT) { T.y = 0u; G.y = 0u; sp = 0; parked = 0; }
                     }
+                };
+                if (OPT & 16) {
+                    // unrolled twice, the two row-0 register sets swapping roles: no copy of the requested row per triangle (5 of the loop's
+                    // 56 instructions); C5 3 659 -> 3 714, C3 3 476 -> 3 506, C4 unchanged (profiles/r02_explore_park_mask.log)
+                    int tri2; float4 w00;
+                    while (T.y != 0u) {
+                        if (turnedAway()) break;
+                        triStep(tri, v00, tri2, w00);
+                        if (T.y == 0u || turnedAway()) break;
+                        triStep(tri2, w00, tri, v00);
+                    }
+                } else
+                while (T.y != 0u) {
+                    if (turnedAway()) break;
+                    int ntri; float4 n00;
+                    triStep(tri, v00, ntri, n00);
                     v00 = n00; tri = ntri;
                 }
             } else
@@ -485,7 +504,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     // refill below 24 live lanes (the binary kernel and the reference use 20): a wide step is ~3x as many instructions as a
     // binary one, so an idle lane costs more; measured 12 / 16 / 20 / 24 / 28 on C5: 3 119 / 3 205 / 3 203 / 3 241 / 3 175,
     // C3: 3 086 (20) -> 3 153 (24)  (profiles/r01_explore_c{3,5}_wide_threshold.log)
-    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148 || variant == 160 || variant == 162) ? 26 : 24) : ctx->cfg.fetch_threshold;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148 || variant == 160 || variant == 162 || variant == 170) ? 26 : 24) : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
@@ -494,15 +513,17 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     if (flags & B2RT_TRACE_STATS) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->statsDev, 0, 16 * sizeof(unsigned long long), stream));
     switch (variant) {
     default:
-    case 108: return launchWideFlags<256, 4, 4, 1, 8, 0, 6>(ctx, p, flags, stream);    // <= 64 regs, 32 warps/SM; look-ahead triangle loop, 8 stack entries in
-                                                                                       // shared memory; triangle groups turned away below 1/4 of the lanes wait in a
-                                                                                       // one-entry room of their own (PARK), hit mask through PRMT (MASK)
-    case 114: return launchWideFlags<256, 4, 4, 1, 8, 128, 6>(ctx, p, flags, stream);  // 108 with 128-ray block claims: batches above 24 Mi rays
+    case 108: return launchWideFlags<256, 4, 4, 1, 8, 0, 22>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM; look-ahead triangle loop unrolled twice, 8 stack
+                                                                                       // entries in shared memory; triangle groups turned away below 1/4 of the lanes
+                                                                                       // wait in a one-entry room of their own (PARK), hit mask through PRMT (MASK)
+    case 114: return launchWideFlags<256, 4, 4, 1, 8, 128, 22>(ctx, p, flags, stream); // 108 with 128-ray block claims: batches above 24 Mi rays
 #ifdef B2RT_EXPLORE
     // shapes measured and not shipped; build with -DB2RT_EXPLORE to get them back
     case 160: return launchWideFlags<256, 4, 4, 1, 8, 128, 14>(ctx, p, flags, stream);   // 114 with two waiting-room entries: C5 3 585 -> 3 480, C3 3 434 -> 3 344
     case 161: return launchWideFlags<256, 4, 4, 1, 8, 0, 14>(ctx, p, flags, stream);     // 108 with two
     case 162: return launchWideFlags<256, 4, 3, 1, 8, 128, 14>(ctx, p, flags, stream);   //   ... threshold 1/3
+    case 170: return launchWideFlags<256, 4, 4, 1, 8, 128, 6>(ctx, p, flags, stream);    // 114 with the triangle loop not unrolled: C5 3 714 -> 3 659, C3 3 506 -> 3 476
+    case 171: return launchWideFlags<256, 4, 4, 1, 8, 0, 6>(ctx, p, flags, stream);      // 108 ...
     case 118: return launchWideFlags<256, 4, 5, 1, 8>(ctx, p, flags, stream);            // variant 108 until the end of round 2: groups pushed on the stack, threshold 1/5
     case 124: return launchWideFlags<256, 4, 5, 1, 8, 128>(ctx, p, flags, stream);       // variant 114 until then
     case 142: return launchWideFlags<256, 4, 5, 1, 8, 128, 2>(ctx, p, flags, stream);    // 124 + MASK
