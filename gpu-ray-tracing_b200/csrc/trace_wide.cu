@@ -93,6 +93,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                                                         // costs more than those pushes: C5 3 585 -> 3 480)
     uint2* s_park = s_wideStack + SSLOTS * BLOCK + threadIdx.x;
     int parked = 0;                                     // groups of this lane in the waiting room
+    // OPT bit 5 (SCAN, CLAIM > 0 only): a claimed block of rays is classified at once; see the fetch
+    constexpr bool SCAN = (OPT & 32) != 0 && CLAIM > 0;
+    unsigned* s_live = reinterpret_cast<unsigned*>(s_wideStack + (SSLOTS + (PARK ? kParkDepth : 0)) * BLOCK) + (threadIdx.x >> 5) * (CLAIM > 0 ? CLAIM : 1);
     auto storeResult = [](const WideParams& q, unsigned rayidx, int id, float t, float u, float v) { storeResultT<BARY>(q, rayidx, id, t, u, v); };
     const int lane = threadIdx.x & 31;
     // Traversal stack: the first SSLOTS entries in shared memory (slot k of this thread at s_stack[k * BLOCK]: consecutive
@@ -170,6 +173,32 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                     b = __shfl_sync(kFullMask, b, 0);
                     if (STATS && lane == 0) stFetches++;
                     if (b >= (unsigned)p.numRays) { poolEmpty = true; break; }
+                    if (SCAN) {
+                        // The whole block is looked at once, all lanes wide: tmin and tmax of every ray (which also brings the rays'
+                        // sectors into L1), degenerate rays (tmax < tmin: the samples of a primary ray that hit nothing, 52 % of the C5
+                        // batch, in runs of 86) answered here, the indices of the others written to the warp's list.  Refills then
+                        // hand out live rays only: no refill round that fills no lane.  C5 3 719 -> 3 785 Mrays/s, node-loop SIMD efficiency
+                        // 82.6 -> 85.5 %; the refill threshold stays at 26 (22: 3 699, 24: 3 767, 28: 3 759, 30: 3 657).
+                        const unsigned n = min((unsigned)kClaim, (unsigned)p.numRays - b);
+                        unsigned live = 0;
+#pragma unroll
+                        for (int k = 0; k < kClaim / 32; k++) {
+                            const unsigned off = 32u * k + lane;
+                            bool ok = false;
+                            if (off < n) {
+                                const float* r = reinterpret_cast<const float*>(p.rays + 2 * (size_t)(b + off));
+                                const float tmn = __ldg(r + 3), tmx = __ldg(r + 7);
+                                ok = !(tmx < tmn);
+                                if (!ok) storeResult(p, b + off, -1, tmx, 0.0f, 0.0f);
+                            }
+                            const unsigned m = __ballot_sync(kFullMask, ok);
+                            if (ok) s_live[live + __popc(m & ((1u << lane) - 1u))] = b + off;
+                            live += __popc(m);
+                        }
+                        __syncwarp();
+                        blkBase = 0u; blkLeft = live;
+                        if (live == 0u) continue;                   // a block of misses only: claim the next one
+                    } else {
                     blkBase = b;
                     blkLeft = min((unsigned)kClaim, (unsigned)p.numRays - b);
                     // rays [b + 32, b + claim): 32 bytes each, one 128-byte line per four rays
@@ -178,6 +207,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                         const unsigned r = b + 32u + 4u * (lane + 32u * k);
                         if (4 * (lane + 32 * k) < kClaim - 32 && r < (unsigned)p.numRays)
                             asm volatile("prefetch.global.L1 [%0];" :: "l"(p.rays + 2 * (size_t)r));
+                    }
                     }
                 }
                 numT = min(numT, blkLeft);
@@ -193,7 +223,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             }
             if (!active) {
                 const unsigned rank = __popc(maskT & ((1u << lane) - 1u));
-                const unsigned idx = base + rank;
+                const unsigned idx = (SCAN && rank < numT) ? s_live[base + rank] : base + rank;
                 if (rank < numT && idx < (unsigned)p.numRays) {
                     float4 o, d;
                     if (p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
@@ -433,7 +463,8 @@ static int launchWideOne(b2rt_ctx* ctx, WideParams& p, cudaStream_t stream)
 {
     auto kern = traceWideKernel<ANY_HIT, BARY, STATS, BLOCK, MIN_BLOCKS, POSTPONE, LEAF, SSLOTS, WT, CLAIM, OPT>;
     int blocksPerSm = 0;
-    const size_t smem = (size_t)(SSLOTS + ((OPT & 4) ? ((OPT & 8) ? 2 : 1) : 0)) * BLOCK * sizeof(uint2);
+    const size_t smem = (size_t)(SSLOTS + ((OPT & 4) ? ((OPT & 8) ? 2 : 1) : 0)) * BLOCK * sizeof(uint2)
+                      + (((OPT & 32) && CLAIM > 0) ? (size_t)(BLOCK / 32) * CLAIM * sizeof(unsigned) : 0);
     { const int rc = kernelOccupancy(ctx, kern, BLOCK, smem, &blocksPerSm); if (rc) return rc; }
     if (blocksPerSm < 1) return setError(ctx, B2RT_ERR_CUDA, "wide trace kernel does not fit on an SM");
     if (ctx->cfg.blocks_per_sm > 0 && ctx->cfg.blocks_per_sm < blocksPerSm) blocksPerSm = ctx->cfg.blocks_per_sm;
@@ -504,7 +535,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     // refill below 24 live lanes (the binary kernel and the reference use 20): a wide step is ~3x as many instructions as a
     // binary one, so an idle lane costs more; measured 12 / 16 / 20 / 24 / 28 on C5: 3 119 / 3 205 / 3 203 / 3 241 / 3 175,
     // C3: 3 086 (20) -> 3 153 (24)  (profiles/r01_explore_c{3,5}_wide_threshold.log)
-    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148 || variant == 160 || variant == 162 || variant == 170) ? 26 : 24) : ctx->cfg.fetch_threshold;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148 || variant == 160 || variant == 162 || variant == 170 || variant == 180 || variant == 181) ? 26 : 24) : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
@@ -516,12 +547,17 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     case 108: return launchWideFlags<256, 4, 4, 1, 8, 0, 22>(ctx, p, flags, stream);   // <= 64 regs, 32 warps/SM; look-ahead triangle loop unrolled twice, 8 stack
                                                                                        // entries in shared memory; triangle groups turned away below 1/4 of the lanes
                                                                                        // wait in a one-entry room of their own (PARK), hit mask through PRMT (MASK)
-    case 114: return launchWideFlags<256, 4, 4, 1, 8, 128, 22>(ctx, p, flags, stream); // 108 with 128-ray block claims: batches above 24 Mi rays
+    case 114: return launchWideFlags<256, 4, 4, 1, 8, 128, 54>(ctx, p, flags, stream); // 108 with 128-ray block claims, each block classified at once (SCAN):
+                                                                                       // batches above 24 Mi rays
 #ifdef B2RT_EXPLORE
     // shapes measured and not shipped; build with -DB2RT_EXPLORE to get them back
     case 160: return launchWideFlags<256, 4, 4, 1, 8, 128, 14>(ctx, p, flags, stream);   // 114 with two waiting-room entries: C5 3 585 -> 3 480, C3 3 434 -> 3 344
     case 161: return launchWideFlags<256, 4, 4, 1, 8, 0, 14>(ctx, p, flags, stream);     // 108 with two
     case 162: return launchWideFlags<256, 4, 3, 1, 8, 128, 14>(ctx, p, flags, stream);   //   ... threshold 1/3
+    case 180: return launchWideFlags<256, 4, 4, 1, 8, 128, 22>(ctx, p, flags, stream);   // 114 without SCAN: C5 3 785 -> 3 719
+    case 181: return launchWideFlags<256, 4, 4, 1, 8, 256, 54>(ctx, p, flags, stream);   // 114 with 256-ray blocks: 3 728
+    case 182: return launchWideFlags<256, 4, 4, 1, 8, 32, 54>(ctx, p, flags, stream);    // 32-ray blocks + SCAN on frame-sized batches: C4 662 -> 636, C3 3 484 -> 3 293
+    case 183: return launchWideFlags<256, 4, 4, 1, 8, 64, 54>(ctx, p, flags, stream);    // 64-ray blocks: C4 609, C3 3 260; 8 Mi-ray shard of C5 3 419 -> 3 437
     case 170: return launchWideFlags<256, 4, 4, 1, 8, 128, 6>(ctx, p, flags, stream);    // 114 with the triangle loop not unrolled: C5 3 714 -> 3 659, C3 3 506 -> 3 476
     case 171: return launchWideFlags<256, 4, 4, 1, 8, 0, 6>(ctx, p, flags, stream);      // 108 ...
     case 118: return launchWideFlags<256, 4, 5, 1, 8>(ctx, p, flags, stream);            // variant 108 until the end of round 2: groups pushed on the stack, threshold 1/5
