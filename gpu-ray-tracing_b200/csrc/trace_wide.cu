@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
     //           of 5 integer operations per child.  C5 3 495 -> 3 524..3 530 Mrays/s (+0.9 %).
     // (OPT bit 0 was HOLD: a lane whose turned-away group is all it has kept it in registers instead of pushing and popping it
     //  every iteration, and requested a group's first row only after the vote.  Same traversal (TRV / IST identical), fewer stack
-    //  operations, 48 more static instructions -- and C5 3 495 -> 3 366: removed.  profiles/r02_explore_park_mask.log)
+    //  operations, 48 more static instructions -- and C5 3 495 -> 3 366: removed.  profiles/r02_explore_c5_last_session.log)
     constexpr bool MASK = (OPT & 2) != 0;
     // OPT bit 2 (PARK, LEAF == 1 only): a triangle group the vote turns away goes to a one-entry waiting room of its own (shared
     //           memory) instead of the traversal stack, and is offered again at EVERY triangle phase in which the lane has no
@@ -181,16 +181,21 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                         // 82.6 -> 85.5 %; the refill threshold stays at 26 (22: 3 699, 24: 3 767, 28: 3 759, 30: 3 657).
                         const unsigned n = min((unsigned)kClaim, (unsigned)p.numRays - b);
                         unsigned live = 0;
+                        float tmn[kClaim / 32 > 0 ? kClaim / 32 : 1], tmx[kClaim / 32 > 0 ? kClaim / 32 : 1];
+#pragma unroll
+                        for (int k = 0; k < kClaim / 32; k++) {             // all loads first: one round trip for the block, not four
+                            const unsigned off = 32u * k + lane;
+                            tmn[k] = 0.0f; tmx[k] = -1.0f;
+                            if (off < n) {
+                                const float* r = reinterpret_cast<const float*>(p.rays + 2 * (size_t)(b + off));
+                                tmn[k] = __ldg(r + 3); tmx[k] = __ldg(r + 7);
+                            }
+                        }
 #pragma unroll
                         for (int k = 0; k < kClaim / 32; k++) {
                             const unsigned off = 32u * k + lane;
-                            bool ok = false;
-                            if (off < n) {
-                                const float* r = reinterpret_cast<const float*>(p.rays + 2 * (size_t)(b + off));
-                                const float tmn = __ldg(r + 3), tmx = __ldg(r + 7);
-                                ok = !(tmx < tmn);
-                                if (!ok) storeResult(p, b + off, -1, tmx, 0.0f, 0.0f);
-                            }
+                            const bool ok = !(tmx[k] < tmn[k]);
+                            if (!ok && off < n) storeResult(p, b + off, -1, tmx[k], 0.0f, 0.0f);
                             const unsigned m = __ballot_sync(kFullMask, ok);
                             if (ok) s_live[live + __popc(m & ((1u << lane) - 1u))] = b + off;
                             live += __popc(m);
@@ -323,7 +328,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
             // node-loop / triangle-loop SIMD efficiency: 1/3 3 257 (66 % / 38 %), 1/4 3 337, 1/5 3 348 (75 % / 28 %), 1/6 3 336, 1/8 3 277,
             // 1/16 3 047 (83 % / 16 %) -- profiles/r02_explore_c5_postpone.log; 1/5 also wins on C4 and C3.  With PARK (turned-away
             // groups wait in a room of their own and the lane traverses on) the balance moves: 1/5 3 523 (84 % / 29 %), 1/4 3 557
-            // (83 % / 32 %), 1/3 3 548 (79 % / 39 %), 1/2 3 342 (69 % / 52 %) -- profiles/r02_explore_park_mask.log; shipped: 1/4.
+            // (83 % / 32 %), 1/3 3 548 (79 % / 39 %), 1/2 3 342 (69 % / 52 %) -- profiles/r02_explore_c5_last_session.log; shipped: 1/4.
             if (PARK && parked && T.y == 0u) { parked--; T = s_park[(kParkDepth == 1 ? 0 : parked) * BLOCK]; }      // no fresh group: offer the parked one
             const int lanesHere = __popc(__activemask());
             if (LEAF == 1) {
@@ -369,7 +374,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 };
                 if (OPT & 16) {
                     // unrolled twice, the two row-0 register sets swapping roles: no copy of the requested row per triangle (5 of the loop's
-                    // 56 instructions); C5 3 659 -> 3 714, C3 3 476 -> 3 506, C4 unchanged (profiles/r02_explore_park_mask.log)
+                    // 56 instructions); C5 3 659 -> 3 714, C3 3 476 -> 3 506, C4 unchanged (profiles/r02_explore_c5_last_session.log)
                     int tri2; float4 w00;
                     while (T.y != 0u) {
                         if (turnedAway()) break;
