@@ -540,7 +540,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     // refill below 24 live lanes (the binary kernel and the reference use 20): a wide step is ~3x as many instructions as a
     // binary one, so an idle lane costs more; measured 12 / 16 / 20 / 24 / 28 on C5: 3 119 / 3 205 / 3 203 / 3 241 / 3 175,
     // C3: 3 086 (20) -> 3 153 (24)  (profiles/r01_explore_c{3,5}_wide_threshold.log)
-    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148 || variant == 160 || variant == 162 || variant == 170 || variant == 180 || variant == 181) ? 26 : 24) : ctx->cfg.fetch_threshold;
+    p.fetchThreshold = ctx->cfg.fetch_threshold < 0 ? ((variant == 114 || variant == 124 || variant == 142 || variant == 145 || variant == 147 || variant == 148 || variant == 160 || variant == 162 || variant == 170 || variant == 180 || variant == 181 || (variant >= 190 && variant <= 194)) ? 26 : 24) : ctx->cfg.fetch_threshold;
     p.warpCounter = ctx->warpCounter;
     p.stats = ctx->statsDev;
     p.one = 0x3F800000u;
@@ -559,6 +559,11 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
     case 160: return launchWideFlags<256, 4, 4, 1, 8, 128, 14>(ctx, p, flags, stream);   // 114 with two waiting-room entries: C5 3 585 -> 3 480, C3 3 434 -> 3 344
     case 161: return launchWideFlags<256, 4, 4, 1, 8, 0, 14>(ctx, p, flags, stream);     // 108 with two
     case 162: return launchWideFlags<256, 4, 3, 1, 8, 128, 14>(ctx, p, flags, stream);   //   ... threshold 1/3
+    case 190: return launchWideFlags<256, 4, 4, 1, 6, 128, 54>(ctx, p, flags, stream);   // 114 with 6 shared stack slots: C5 3 802 -> 3 801
+    case 191: return launchWideFlags<256, 4, 4, 1, 10, 128, 54>(ctx, p, flags, stream);  //   ... 10: 3 788
+    case 192: return launchWideFlags<256, 4, 4, 1, 12, 128, 54>(ctx, p, flags, stream);  //   ... 12: 3 787
+    case 193: return launchWideFlags<256, 4, 3, 1, 8, 128, 54>(ctx, p, flags, stream);   // 114 with the threshold at 1/3: 3 796
+    case 194: return launchWideFlags<256, 4, 5, 1, 8, 128, 54>(ctx, p, flags, stream);   //   ... 1/5: 3 768
     case 180: return launchWideFlags<256, 4, 4, 1, 8, 128, 22>(ctx, p, flags, stream);   // 114 without SCAN: C5 3 785 -> 3 719
     case 181: return launchWideFlags<256, 4, 4, 1, 8, 256, 54>(ctx, p, flags, stream);   // 114 with 256-ray blocks: 3 728
     case 182: return launchWideFlags<256, 4, 4, 1, 8, 32, 54>(ctx, p, flags, stream);    // 32-ray blocks + SCAN on frame-sized batches: C4 662 -> 636, C3 3 484 -> 3 293
