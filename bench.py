@@ -566,7 +566,11 @@ def product_arm(args):
     # ---- the reference's real frame: everything born on the device, pixels back (Renderer.cc:112-152,242-300) ----
     frame_e2e = None
     if cfg["ray_type"] == "diffuse":
-        frame_e2e = wl.render_frame_e2e(name, scene, frame.cuda_bvh, ctx, device, steps=max(2, min(args.steps, 5)), shard=shard)
+        frame_one = wl.render_frame_e2e(name, scene, frame.cuda_bvh, ctx, device, steps=max(2, min(args.steps, 5)), shard=shard, n_streams=1)
+        frame_e2e = wl.render_frame_e2e(name, scene, frame.cuda_bvh, ctx, device, steps=max(2, min(args.steps, 5)), shard=shard, n_streams=2)
+        # same image either way (pixels are written by disjoint reconstruct launches)
+        assert bool((frame_one.pop("pixels") == frame_e2e.pop("pixels")).all()), "frame: two-stream order changed the image"
+        frame_e2e["ms_per_step_one_stream"] = frame_one["ms_per_step"]
     sampler.stop()
 
     # ---- reduce over ranks ----------------------------------------------------------------------
@@ -654,7 +658,8 @@ def product_arm(args):
         line["e2e"]["frame"] = {
             "value": frame_counted_all / (frame_ms_max * 1e-3) * 1e-6, "unit": "Mrays/s", "ms_per_step": frame_ms_max,
             "h2d_bytes_per_step": frame_e2e["h2d"] * ws, "d2h_bytes_per_step": frame_e2e["d2h"] * ws, "launches_per_step": frame_e2e["launches"],
-            "api": frame_e2e["api"]}
+            "api": frame_e2e["api"],
+            "ms_per_step_one_stream_rank0": frame_e2e["ms_per_step_one_stream"]}
     if ws > 1 and strong:
         t_g = gather_ms_max
         line["with_gather"] = {"value": counted_all / (t_g * 1e-3) * 1e-6, "unit": "Mrays/s", "ms_per_step": t_g,

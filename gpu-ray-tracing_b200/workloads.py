@@ -225,12 +225,16 @@ def _slice_buffer(rb, lo, hi, closest=None):
     return out
 
 
-def render_frame_e2e(name, scene, cuda_bvh, ctx, device, steps=3, shard=(0, 1)):
+def render_frame_e2e(name, scene, cuda_bvh, ctx, device, steps=3, shard=(0, 1), n_streams=2):
     """The reference's real frame, end to end (Renderer::beginFrame / nextBatch / traceBatch / reconstruct,
     Renderer.cc:112-152,242-300): camera -> primary rays generated on the device -> closest-hit trace -> hit count ->
     diffuse batches of at most 2 Mi rays generated on the device from the primary hits -> closest-hit trace -> reconstruct
     -> the frame's pixels copied to the host.  Nothing but the camera goes up; pixels and one counter come down.
-    With shard = (rank, world) this rank renders every world-th 8x8 pixel block.  Wall clock, device idle at both ends."""
+    With shard = (rank, world) this rank renders every world-th 8x8 pixel block.  Wall clock, device idle at both ends.
+    The secondary batches depend on the primary batch only (the reference runs them one after the other because it has one
+    ray buffer and one work counter, Renderer.cc:242-291, kepler_dynamic_fetch.cu:58): with n_streams = 2 they alternate
+    between two ray buffers on two streams, so that one batch's ray generation and the head of its trace run under the tail
+    of the batch before it; n_streams = 1 is the reference's order."""
     from .host import reconstruct
     c = CONFIGS[name]
     w, h = c["size"]
@@ -243,7 +247,8 @@ def render_frame_e2e(name, scene, cuda_bvh, ctx, device, steps=3, shard=(0, 1)):
     origin, m = camera_matrices(scene.camera, w, h)
     far = scene.camera["far"]
     prim = RayBuffer(0, True, device)
-    sec = RayBuffer(0, True, device)
+    secs = [RayBuffer(0, True, device) for _ in range(max(1, n_streams))]
+    streams = [torch.cuda.Stream(device=device) for _ in range(n_streams)] if n_streams > 1 else []
     ntri = scene.getNumTriangles()
     material = torch.full((ntri,), 0xFF808080, dtype=torch.int64, device=device).to(torch.int32)
     shaded = torch.full((ntri,), 0xFFC0C0C0, dtype=torch.int64, device=device).to(torch.int32)
@@ -265,16 +270,24 @@ def render_frame_e2e(name, scene, cuda_bvh, ctx, device, steps=3, shard=(0, 1)):
             src.m_slotToID[:src.getSize()].copy_(prim.m_slotToID[mine])
         tracer.traceBatchAsync(src)
         hits = countHits(src.getResultBuffer_dev(), ctx)                       # Renderer::getTotalNumRays (Renderer.cc:221-238)
-        newBatch, first = True, 0
+        newBatch, first, k = True, 0, 0
+        cur = torch.cuda.current_stream(device)
+        for st in streams:
+            st.wait_stream(cur)                                                 # (countHits above has synchronised already)
         while True:
-            cont, newBatch = raygen.ao(sec, src, scene, samples, far, newBatch)
-            if not cont:
-                break
-            sec.setNeedClosestHit(True)                                         # Renderer.cc:277
-            tracer.traceBatchAsync(sec)
-            n_prim = sec.getSize() // samples
-            reconstruct("diffuse", samples, first, n_prim, src, sec, material, shaded, pixels, ctx)
+            sec = secs[k % len(secs)]
+            with torch.cuda.stream(streams[k % len(streams)] if streams else cur):
+                cont, newBatch = raygen.ao(sec, src, scene, samples, far, newBatch)
+                if not cont:
+                    break
+                sec.setNeedClosestHit(True)                                     # Renderer.cc:277
+                tracer.traceBatchAsync(sec)
+                n_prim = sec.getSize() // samples
+                reconstruct("diffuse", samples, first, n_prim, src, sec, material, shaded, pixels, ctx)
             first += n_prim
+            k += 1
+        for st in streams:
+            cur.wait_stream(st)
         host_pixels.copy_(pixels, non_blocking=True)
         torch.cuda.synchronize()
         if step:
@@ -283,4 +296,5 @@ def render_frame_e2e(name, scene, cuda_bvh, ctx, device, steps=3, shard=(0, 1)):
             launches = ctx.launch_count() - l0
     return {"ms_per_step": float(np.median(times)), "counted": int(counted), "h2d": 19 * 4, "d2h": w * h * 4 // ws + 8, "launches": int(launches),
             "api": "RayGen::primary -> traceBatch -> countHits -> {RayGen::ao (diffuse, 2 Mi-ray batches) -> traceBatch -> reconstruct} -> pixels to the host; "
-                   "wall clock per frame, median of %d" % len(times)}
+                   "wall clock per frame, median of %d; secondary batches alternate between %d stream(s)" % (len(times), max(1, n_streams)),
+            "pixels": host_pixels.clone()}
