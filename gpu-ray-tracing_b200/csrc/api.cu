@@ -366,7 +366,9 @@ int b2rt_trace_host_begin(b2rt_ctx* ctx, const void* raysHost, void* resultsHost
     rc = ensureStage(ctx, slot, rayBytes + resBytes);
     if (rc) return rc;
     // 256 Ki rays per chunk: measured best on C2 (64 Ki 876, 128 Ki 1 055, 192 Ki 1 225, 256 Ki 1 275, 400 K 1 138 Mrays/s
-    // end to end) -- smaller chunks make the launches tail-bound and slower than their own upload
+    // end to end) -- smaller chunks make the launches tail-bound and slower than their own upload.  At most kHostChunks (32)
+    // chunks per batch: what a batch costs beyond its upload is the LAST chunk's trace and download, so a 64 Mi-ray batch goes
+    // in 32 chunks of 2 Mi rays rather than 8 of 8 Mi (see DESIGN.md section 5 for the measured difference).
     int chunks = (int)std::min<int64_t>(b2rt_ctx::kHostChunks, std::max<int64_t>(1, numRays / (256 * 1024)));
     const int64_t per = ((numRays + chunks - 1) / chunks + 31) & ~int64_t(31);
     chunks = (int)((numRays + per - 1) / per);

@@ -64,7 +64,7 @@ struct b2rt_ctx {
     unsigned long long* statsDev = nullptr;     // 16 counters for the instrumented kernel + kTimelineWarps exit times
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // b2rt_trace_host: upload / trace / download pipeline
-    static constexpr int kHostChunks = 8;
+    static constexpr int kHostChunks = 32;
     static constexpr int kHostSlots = 2;        // host batches in flight (b2rt_trace_host_begin / _end)
     cudaStream_t sIn = nullptr, sRun = nullptr, sOut = nullptr;
     struct HostSlot {
