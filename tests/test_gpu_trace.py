@@ -168,6 +168,55 @@ def test_wide_kernel_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     assert (got["id"][5::97] == -1).all() and (got["t"][5::97] == -1.0).all()
 
 
+@pytest.mark.parametrize("n", [1, 31, 127, 128, 129, 4097, 100003])
+def test_block_classification_ragged_batches_and_runs_of_degenerate_rays(b2rt, oracle, ctx, n):
+    """Variant 114 (trace_wide.cu, SCAN): a warp claims 128 rays, answers the degenerate ones (tmax < tmin,
+    RayGenKernels.cu:223) with all lanes at once and hands out the others from a list.  Batches that are not a multiple of
+    the block, runs of degenerate rays as an AO / diffuse batch has them (all samples of a primary ray that hit nothing) --
+    shorter than, equal to and longer than a block -- any-hit and closest-hit: every record written, degenerate rays get
+    (-1, tmax), the others what the binary kernel gives, bit for bit wherever the ids agree."""
+    scene = b2rt.Scene.generate("knot", 40000, 7)
+    bvh = b2rt.BVH(scene)
+    base = _primary_rays(b2rt, oracle, scene, 400, 300)
+    rng = np.random.default_rng(n)
+    rays = base[rng.integers(0, len(base), n)].copy()
+    dead = np.zeros(n, bool)
+    pos = 0
+    while pos < n:                                              # runs: live 1..200 rays, then dead 1..300 rays
+        pos += int(rng.integers(1, 200))
+        run = int(rng.integers(1, 300))
+        dead[pos:pos + run] = True
+        pos += run
+    if n > 300:
+        dead[128:384] = True                                    # two whole blocks of misses: a claim that finds nothing to hand out
+    rays["tmax"][dead] = rays["tmin"][dead] - 0.25
+    tracer = b2rt.CudaTracer(ctx)
+    tracer.setBVH(b2rt.CudaBVH(bvh))
+    for closest in (True, False):
+        rb = b2rt.RayBuffer(closestHit=closest)
+        rb.setRays(rays)
+        rb.setNeedClosestHit(closest)
+        out = {}
+        for variant in (1, 114):
+            rb.getResultBuffer_dev().fill_(0x7E7E7E7E)          # a record nobody writes would keep this
+            ctx.set_trace_config(variant=variant)
+            try:
+                tracer.traceBatch(rb)
+            finally:
+                ctx.set_trace_config()
+            out[variant] = rb.getResults().copy()
+        got, want = out[114], out[1]
+        assert (got["id"] != 0x7E7E7E7E).all(), "%d records were never written" % int((got["id"] == 0x7E7E7E7E).sum())
+        assert (got["id"][dead] == -1).all() and (got["t"][dead] == rays["tmax"][dead]).all()
+        live = ~dead
+        if closest:
+            same = got["id"] == want["id"]
+            assert same[live].mean() >= ID_AGREE if live.sum() >= 20000 else (~same[live]).sum() <= 2
+            assert (got["t"][same] == want["t"][same]).all()
+        else:
+            assert ((got["id"] >= 0) == (want["id"] >= 0)).all()
+
+
 @pytest.mark.parametrize("variant", [1, 9])
 @pytest.mark.parametrize("kind,ntris", [("interior", 30000), ("knot", 40000)])
 @pytest.mark.parametrize("count", [1, 37, 4097, 0])
