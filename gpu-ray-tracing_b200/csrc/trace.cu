@@ -617,10 +617,12 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
             // ... unless the collapsed tree is too deep for that kernel's stack (a degenerate caller-built BVH): stay binary
             const int rc = ensureWide(ctx);
             if (rc) return rc;
-            // block claims (variant 114) above 24 Mi rays: a warp can hold 127 unstarted rays when the pool runs dry, 7 % of an
-            // 8 Mi-ray batch over 4 736 warps -- measured on shards of the C5 batch: 8 Mi rays 3 209 (108) vs 3 092 (114), 16 Mi 3 307 vs
-            // 3 300, 32 Mi 3 385 vs 3 432, 64 Mi 3 398 vs 3 495 Mrays/s (profiles/r02_explore_c5_shards.log)
-            if (ctx->wideMaxDepth <= kWideMaxDepth) variant = (numRays > (24 << 20)) ? 114 : 108;
+            // block claims (variant 114) above 12 Mi rays: a warp can hold 127 unstarted rays when the pool runs dry, 7 % of an
+            // 8 Mi-ray batch over 4 736 warps -- measured on shards of the C5 batch with the kernels as shipped (108 vs 114): 8 Mi rays
+            // 3 419 vs 3 310, 16 Mi 3 520 vs 3 570, 21 Mi 3 536 vs 3 605, 32 Mi 3 598 vs 3 725 Mrays/s (the whole 64 Mi batch: 3 802 with 114)
+            // (profiles/r02_explore_c5_last_session.log; before block classification the crossover was at 24 Mi:
+            // r02_explore_c5_shards.log)
+            if (ctx->wideMaxDepth <= kWideMaxDepth) variant = (numRays > (12 << 20)) ? 114 : 108;
         }
     }
     if (variant >= 100) return launchTraceWide(ctx, rays, results, numRays, flags, variant, stream);

@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 // the index and the ray at hand.  Measured on the C5 batch (profiles/r02_explore_c5_claims.log): 64 rays per claim +0.7 %,
                 // 128 +2.4 %, 256 +2.0 %; with the refill threshold at 26 instead of 24 another +0.6 %.  A warp holds up to claim - 1
                 // unstarted rays when the pool runs dry, which lengthens the tail of a frame-sized launch (C4 -14 %, C3 -10 %): used for
-                // batches above 24 Mi rays only (launchTrace).
+                // batches above 12 Mi rays only (launchTrace; 24 Mi before block classification).
                 if (blkLeft == 0u) {
                     unsigned b = 0;
                     if (lane == 0) b = (unsigned)atomicAdd(p.warpCounter, kClaim);
@@ -553,7 +553,7 @@ int launchTraceWide(b2rt_ctx* ctx, const void* rays, void* results, int64_t numR
                                                                                        // entries in shared memory; triangle groups turned away below 1/4 of the lanes
                                                                                        // wait in a one-entry room of their own (PARK), hit mask through PRMT (MASK)
     case 114: return launchWideFlags<256, 4, 4, 1, 8, 128, 54>(ctx, p, flags, stream); // 108 with 128-ray block claims, each block classified at once (SCAN):
-                                                                                       // batches above 24 Mi rays
+                                                                                       // batches above 12 Mi rays
 #ifdef B2RT_EXPLORE
     // shapes measured and not shipped; build with -DB2RT_EXPLORE to get them back
     case 160: return launchWideFlags<256, 4, 4, 1, 8, 128, 14>(ctx, p, flags, stream);   // 114 with two waiting-room entries: C5 3 585 -> 3 480, C3 3 434 -> 3 344
