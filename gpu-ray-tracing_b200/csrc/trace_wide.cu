@@ -15,6 +15,13 @@
 // A node step pops the highest hit bit of G -- bit position = 24 + (slot XOR ray octant), so siblings
 // come out front to back -- pushes the rest of G, tests the eight child boxes of that node and forms
 // the next G and T from the resulting 32-bit hit mask.
+//
+// Shape of the shipped kernels (variants 108 / 114, launchTraceWide below; every choice with its measurement next to the code and in
+// DESIGN.md section 4): 256-thread CTAs, four per SM at 64 registers; 8 stack entries per lane in shared memory, the rest in local
+// memory; the triangle loop requests row 0 of a group's next triangle before it tests the current one and is unrolled twice; a
+// triangle group that fewer than a quarter of the warp's lanes could be tested with waits in a one-entry room per lane (PARK) while
+// the lane traverses on; rays and records move with the streaming cache policy; for batches above 12 Mi rays a warp claims 128
+// rays per atomic and classifies the block at once (SCAN), smaller batches take exactly as many rays as there are idle lanes.
 #include "common.cuh"
 
 namespace b2rt {
@@ -247,6 +254,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
         }
         const int threshold = poolEmpty ? 0 : p.fetchThreshold;
 
+        // `if (active) for (;;)` with explicit breaks, not `while (active)`: the loop leaves only through the breaks below (each sets what it
+        // has to), and with the flag out of the loop condition ptxas drops 39 register moves, 12 of them at the loop top of every
+        // iteration -- C5 3 585 -> 3 645 Mrays/s, C4 628 -> 638 (-DB2RT_LOOP_WHILE brings the old shape back)
 #ifndef B2RT_LOOP_WHILE
         if (active) for (;;) {
 #else
