@@ -630,7 +630,9 @@ def product_arm(args):
         "achieved": issue["achieved"] if issue else None, "peak": issue_peak * 1e-9, "frac": issue["frac"] if issue else None,
         "traffic": traffic, "kernel": "traceWideKernel" if wide else "traceKernel", "avg_launch_ms": avg_launch_ms,
         "how": "executed warp-instructions per ray (ncu smsp__inst_executed.sum of this kernel on this workload, profiles/traffic.json) x rays per "
-               "launch / live CUDA-event launch time, against 4 schedulers x %d SMs x the SM clock sampled during the timed region" % sm_count,
+               "launch / live CUDA-event launch time, against 4 schedulers x %d SMs x the SM clock sampled during the timed region" % sm_count
+               + ("" if ws == 1 else "; the per-ray instruction count is the one-GPU capture's (whole batch, block-claim kernel): a shard below 12 Mi rays runs "
+                                     "the kernel without block claims, which executes a few per cent more per ray"),
         "fp32": {"inst_per_s": fp32_rate, "peak_inst_per_s": sm_count * 128 * sm_hz, "frac": fp32_rate / (sm_count * 128 * sm_hz),
                  "how": "SURVEY 8(d) algorithmic FP32 instructions (canonical traversal) against 128 lanes per SM"},
         "hbm": hbm,
