@@ -22,6 +22,12 @@
 
 namespace b2rt {
 
+#ifdef B2RT_EXPLORE
+constexpr bool kAlwaysStream = false;       // B2RT_TUNE_NO_STREAM is an A/B switch in -DB2RT_EXPLORE builds only (trace_wide.cu)
+#else
+constexpr bool kAlwaysStream = true;
+#endif
+
 struct TraceParams {
     const float4* __restrict__ rays;
     int4* __restrict__ results;
@@ -151,11 +157,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                 const int id = (hitIndex == -1) ? -1 : __ldg(p.triIndex + hitIndex);
                 if (BARY) {
                     const int4 r = make_int4(id, __float_as_int(hitT), __float_as_int(hitU), __float_as_int(hitV));
-                    if (p.streamRays) __stcs(p.results + rayidx, r); else p.results[rayidx] = r;
+                    if (kAlwaysStream || p.streamRays) __stcs(p.results + rayidx, r); else p.results[rayidx] = r;
                 } else {
                     int2* dst = reinterpret_cast<int2*>(p.results + rayidx);      // 8 of the record's 16 bytes (CudaTracerKernels.hh:197)
                     const int2 r = make_int2(id, __float_as_int(hitT));
-                    if (p.streamRays) __stcs(dst, r); else *dst = r;
+                    if (kAlwaysStream || p.streamRays) __stcs(dst, r); else *dst = r;
                 }
             }
             rayidx = -1;
@@ -185,7 +191,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                 if (idx < (unsigned)p.numRays) {
                     rayidx = (int)idx;
                     float4 o, d;
-                    if (p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
+                    if (kAlwaysStream || p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
                     else { o = ldg4(p.rays + 2 * (size_t)idx); d = ldg4(p.rays + 2 * (size_t)idx + 1); }
                     origx = o.x; origy = o.y; origz = o.z; tmin = o.w;
                     dirx = d.x; diry = d.y; dirz = d.z; hitT = d.w;

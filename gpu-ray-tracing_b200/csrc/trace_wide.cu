@@ -45,6 +45,13 @@ struct WideParams {
 // those pushes cannot be refused, so triangle groups are postponed only below WideParams::pushLimit = capacity - depth - 1 and
 // the launcher sends trees deeper than capacity - 2 to the binary kernel (trace.cu:launchTrace).
 constexpr int kWideStack = 48;
+// The streaming policy for rays and records is an A/B switch (B2RT_TUNE_NO_STREAM) only in -DB2RT_EXPLORE builds: as a run-time
+// flag it doubles every ray load and record store of the refill path into two predicated forms.
+#ifdef B2RT_EXPLORE
+constexpr bool kAlwaysStream = false;
+#else
+constexpr bool kAlwaysStream = true;
+#endif
 constexpr unsigned kFullMask = 0xffffffffu;
 
 
@@ -64,11 +71,11 @@ __device__ __forceinline__ void storeResultT(const WideParams& p, unsigned rayid
 {
     if (BARY) {
         const int4 r = make_int4(id, __float_as_int(t), __float_as_int(u), __float_as_int(v));
-        if (p.streamRays) __stcs(p.results + rayidx, r); else p.results[rayidx] = r;
+        if (kAlwaysStream || p.streamRays) __stcs(p.results + rayidx, r); else p.results[rayidx] = r;
     } else {
         int2* dst = reinterpret_cast<int2*>(p.results + rayidx);           // 8 of the record's 16 bytes (CudaTracerKernels.hh:197)
         const int2 r = make_int2(id, __float_as_int(t));
-        if (p.streamRays) __stcs(dst, r); else *dst = r;
+        if (kAlwaysStream || p.streamRays) __stcs(dst, r); else *dst = r;
     }
 }
 
@@ -238,7 +245,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceWideKernel(const WideP
                 const unsigned idx = (SCAN && rank < numT) ? s_live[base + rank] : base + rank;
                 if (rank < numT && idx < (unsigned)p.numRays) {
                     float4 o, d;
-                    if (p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
+                    if (kAlwaysStream || p.streamRays) { o = __ldcs(p.rays + 2 * (size_t)idx); d = __ldcs(p.rays + 2 * (size_t)idx + 1); }
                     else { o = ldg4(p.rays + 2 * (size_t)idx); d = ldg4(p.rays + 2 * (size_t)idx + 1); }
                     takeRay(idx, o, d);
                 }

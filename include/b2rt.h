@@ -71,7 +71,8 @@ typedef struct {
     int l2_prefetch;            /* reserved (was: pull the BVH into L2 at launch start; measured no gain, removed); ignored */
     unsigned tune;              /* B2RT_TUNE_* bits that switch single design decisions OFF for A/B measurements; 0 = as shipped */
 } b2rt_trace_config;
-#define B2RT_TUNE_NO_STREAM      1u  /* rays / records through the normal cache policy instead of evict-first (ld.cs / st.cs) */
+#define B2RT_TUNE_NO_STREAM      1u  /* rays / records through the normal cache policy instead of evict-first (ld.cs / st.cs);
+                                         honoured by -DB2RT_EXPLORE builds only: shipped kernels always stream */
 #define B2RT_TUNE_GREEDY_WIDE    4u  /* 8-wide form: round-1 greedy top-down collapse instead of the SAH-optimal one; takes effect
                                         at the next b2rt_set_bvh */
 #define B2RT_TUNE_DEFAULT_CARVEOUT 16u /* leave the shared-memory / L1 split to the driver instead of asking for the resident CTAs' need;
