@@ -384,7 +384,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
 
             // postponed leaves
             while (leafAddr < 0) {
-                if (LEAF == 1) {
+                if (LEAF >= 1) {
+                    constexpr bool UNROLL = (LEAF == 2);
                     // Row 0 of the NEXT triangle (or the terminator) is requested before the current triangle is tested: the
                     // terminator test and the distance test of the next step need nothing else, so they no longer wait a whole
                     // fetch behind the current test (ncu source page of the LEAF == 0 kernel: 14 % of all stall samples sit on the
@@ -395,12 +396,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                     // operations in the same order as LEAF == 0: the same bits.
                     int triAddr = ~leafAddr;
                     float4 v00 = ldg4(p.woop + triAddr);
-                    while (__float_as_int(v00.x) != (int)0x80000000) {
-                        const float4 n00 = ldg4(p.woop + triAddr + 3);
-                        const float4 v11 = ldg4(p.woop + triAddr + 1), v22 = ldg4(p.woop + triAddr + 2);
+                    // tests the triangle at `addr` (row 0 in c00) and requests row 0 of the next one into n00; true: an any-hit ray is done
+                    auto leafStep = [&](const int addr, const float4& c00, float4& n00) -> bool {
+                        n00 = ldg4(p.woop + addr + 3);
+                        const float4 v11 = ldg4(p.woop + addr + 1), v22 = ldg4(p.woop + addr + 2);
                         if (STATS) { const unsigned am = __activemask(); stTriLanes++; if (lane == __ffs(am) - 1) stTriIters++; }
-                        const float Oz = woopPlane(-origx, -origy, -origz, v00);
-                        const float invDz = rcp_approx(woopDot(dirx, diry, dirz, v00));
+                        const float Oz = woopPlane(-origx, -origy, -origz, c00);
+                        const float invDz = rcp_approx(woopDot(dirx, diry, dirz, c00));
                         const float t = fmulFtz(Oz, invDz);
                         const float Ox = woopPlane(origx, origy, origz, v11);
                         const float Dx = woopDot(dirx, diry, dirz, v11);
@@ -408,12 +410,29 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) traceKernel(const TracePara
                         const float Oy = woopPlane(origx, origy, origz, v22);
                         const float Dy = woopDot(dirx, diry, dirz, v22);
                         const float v = ffmaFtz(t, Dy, Oy);
-                        if (woopAccept<WT>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, triAddr, hitIndex, p.triIndex)) {
-                            hitT = t; hitIndex = triAddr;
+                        if (woopAccept<WT>(t, tmin, hitT, u, v, v11, v22, WtRay{ origx, origy, origz, dirx, diry, dirz }, addr, hitIndex, p.triIndex)) {
+                            hitT = t; hitIndex = addr;
                             if (WT) cullT = watertightCull(t);
                             if (BARY) { hitU = u; hitV = v; }
-                            if (ANY_HIT) { nodeAddr = kSentinel; break; }
+                            if (ANY_HIT) { nodeAddr = kSentinel; return true; }
                         }
+                        return false;
+                    };
+                    if (UNROLL) {
+                        // unrolled twice, the two row-0 register sets swapping roles: no copy of the requested row per triangle (4 of the
+                        // loop's 41 instructions); C1 3 261 -> 3 319 Mrays/s, C2 within noise
+                        float4 w00;
+                        while (__float_as_int(v00.x) != (int)0x80000000) {
+                            if (leafStep(triAddr, v00, w00)) break;
+                            triAddr += 3;
+                            if (__float_as_int(w00.x) == (int)0x80000000) break;
+                            if (leafStep(triAddr, w00, v00)) break;
+                            triAddr += 3;
+                        }
+                    } else
+                    while (__float_as_int(v00.x) != (int)0x80000000) {
+                        float4 n00;
+                        if (leafStep(triAddr, v00, n00)) break;
                         v00 = n00; triAddr += 3;
                     }
                 } else {
@@ -635,9 +654,14 @@ int launchTrace(b2rt_ctx* ctx, const void* rays, void* results, int64_t numRays,
     switch (variant) {
     default:
     case 1: return launchFlags<12, 256, 4>(ctx, p, flags, stream);      // four 256-thread CTAs per SM (<= 64 regs), reference-shaped leaf loop
-    case 8: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream);  // one 1024-thread CTA per SM, 2048-node shared top of the tree, look-ahead leaf loop
-    case 9: return launchFlags<12, 512, 2, 1>(ctx, p, flags, stream);   // two 512-thread CTAs per SM, look-ahead leaf loop (any-hit batches)
-    case 10: return launchFlags<12, 256, 4, 1>(ctx, p, flags, stream);  // variant 1 with the look-ahead leaf loop
+    case 8: return launchFlags<12, 1024, 1, 2>(ctx, p, flags, stream);  // one 1024-thread CTA per SM, 2048-node shared top of the tree, look-ahead leaf loop unrolled twice
+    case 9: return launchFlags<12, 512, 2, 2>(ctx, p, flags, stream);   // two 512-thread CTAs per SM, the same leaf loop (any-hit batches)
+    case 10: return launchFlags<12, 256, 4, 2>(ctx, p, flags, stream);  // variant 1 with that leaf loop
+    case 11: return launchFlags<12, 256, 4, 1>(ctx, p, flags, stream);  // 10 with the look-ahead leaf loop not unrolled (LEAF == 1): the bit-identity test's third shape
+#ifdef B2RT_EXPLORE
+    case 18: return launchFlags<12, 1024, 1, 1>(ctx, p, flags, stream); // 8 not unrolled: C1 3 319 -> 3 261, C2 within noise (profiles/r02_explore_c5_last_session.log)
+    case 19: return launchFlags<12, 512, 2, 1>(ctx, p, flags, stream);  // 9 not unrolled
+#endif
 #ifdef B2RT_EXPLORE
     // shapes measured in round 1 and not shipped; build with -DB2RT_EXPLORE to get them back
     case 0: return launchFlags<12, 256, 5>(ctx, p, flags, stream);   // <= 48 regs, 40 warps/SM

@@ -40,7 +40,7 @@ def _check_closest(oracle, bvh_arrays, rays, got, ref=None, agree=ID_AGREE):
 
 
 @pytest.mark.parametrize("kind,ntris", [("blob", 20000), ("interior", 30000), ("knot", 40000), ("strands", 30000)])
-@pytest.mark.parametrize("variant", [1, 8, 9, 10])
+@pytest.mark.parametrize("variant", [1, 8, 9, 10, 11])
 def test_primary_closest_hit(b2rt, oracle, ctx, kind, ntris, variant):
     scene = b2rt.Scene.generate(kind, ntris, 20260101)
     bvh = b2rt.BVH(scene)
@@ -397,9 +397,10 @@ def test_traces_on_two_streams_overlap_safely(b2rt, oracle, ctx):
                 assert same.mean() >= 0.999 and (got["t"][same] == want["t"][same]).all()
 
 
-@pytest.mark.parametrize("pair", [(1, 10)])
+@pytest.mark.parametrize("pair", [(1, 10), (1, 11), (10, 11)])
 def test_lookahead_leaf_loop_returns_the_same_bits(b2rt, oracle, ctx, pair):
-    """LEAF = 1 (row 0 of the next triangle requested ahead, Woop test without early-outs; trace.cu) performs the same
+    """LEAF = 1 / 2 (row 0 of the next triangle requested ahead, Woop test without early-outs; 2 = that loop unrolled twice:
+    variants 11 and 10; trace.cu) performs the same
     floating-point operations in the same order as the reference-shaped loop: wherever both kernels report the same
     triangle, t, u and v must be identical bit for bit, and the ids may differ only between triangles at one distance."""
     scene = b2rt.Scene.generate("interior", 30000, 7)
